@@ -1,0 +1,274 @@
+// cg_api.cu -- the C ABI of libcanarygate.so (see include/canary_gate.h) and the small
+// standalone kernels (gate, replay).  Build: nvcc -gencode arch=compute_100a,code=sm_100a
+// -fmad=false (no FMA contraction: the reference computes in Python floats).
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <atomic>
+
+#include "../../include/canary_gate.h"
+#include "cg_general.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(CG_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+constexpr int kMaxSmem = 232448;   // 227 KB opt-in limit per CTA on sm_100
+
+size_t elem_size(const cg_params* p) { return p->dtype == CG_F32 ? 4 : 8; }
+
+int check_params(const cg_params* p) {
+    if (!p) return fail(CG_EINVAL, "params is NULL");
+    if (p->struct_bytes != (int32_t)sizeof(cg_params))
+        return fail(CG_EINVAL, "cg_params.struct_bytes = %d, library expects %d (ABI mismatch)",
+                    p->struct_bytes, (int)sizeof(cg_params));
+    if (p->dtype != CG_F64 && p->dtype != CG_F32) return fail(CG_EINVAL, "dtype must be CG_F64 or CG_F32");
+    if (p->n_samples < 1) return fail(CG_EINVAL, "n_samples must be >= 1");
+    if (p->row_pitch < p->n_samples) return fail(CG_EINVAL, "row_pitch < n_samples");
+    if (((size_t)p->row_pitch * elem_size(p)) % 16 != 0)
+        return fail(CG_EINVAL, "row pitch (%d elements) must be a multiple of 16 bytes", p->row_pitch);
+    if (p->n_scalar < 0 || p->n_scalar > CG_MAX_SCALAR) return fail(CG_EINVAL, "n_scalar out of range [0,%d]", CG_MAX_SCALAR);
+    if (p->n_buckets < 0 || p->n_buckets > 1024) return fail(CG_EINVAL, "n_buckets out of range [0,1024]");
+    if (p->period_ms <= 0 || p->window_ms <= 0 || p->tick_step_ms <= 0)
+        return fail(CG_EINVAL, "period_ms, window_ms and tick_step_ms must be positive");
+    if (p->n_ticks < 0) return fail(CG_EINVAL, "n_ticks must be >= 0");
+    if (p->n_q < 0 || p->n_q > CG_MAX_Q) return fail(CG_EINVAL, "n_q out of range [0,%d]", CG_MAX_Q);
+    if (p->n_buckets > 0 && p->n_q < 1) return fail(CG_EINVAL, "n_q must be >= 1 when n_buckets > 0");
+    if (p->n_buckets == 0 && p->n_q != 0) return fail(CG_EINVAL, "n_q must be 0 when n_buckets == 0");
+    if (p->n_q > 0 && (p->gate_q < 0 || p->gate_q >= p->n_q)) return fail(CG_EINVAL, "gate_q out of range");
+    if (p->checks & ~7) return fail(CG_EINVAL, "checks has unknown bits");
+    if (p->max_attempts < 1 || p->step < 1 || p->max_traffic < 1 || p->interval_ticks < 0 ||
+        p->attempt_delay_ticks < 0 || p->init_current < 0)
+        return fail(CG_EINVAL, "bad schedule constants");
+    if (p->attempt_delay_ticks == 0 && p->interval_ticks == 0)
+        return fail(CG_EINVAL, "schedule never advances (both delays are 0 ticks)");
+    return CG_OK;
+}
+
+int check_aligned(const void* ptr, const char* name) {
+    if (((uintptr_t)ptr) & 15) return fail(CG_EINVAL, "%s must be 16-byte aligned", name);
+    return CG_OK;
+}
+
+struct GeneralPlan {
+    cg::GeneralArgs args;
+    int grid, block;
+};
+
+int plan_general(const cg_params* p, int64_t n_pairs, GeneralPlan* plan) {
+    cg::GeneralArgs& a = plan->args;
+    memset(&a, 0, sizeof(a));
+    a.p = *p;
+    a.n_pairs = n_pairs;
+    const size_t esz = elem_size(p);
+    size_t off = (size_t)(p->n_scalar + p->n_buckets) * p->row_pitch * esz;
+    off = (off + 15) & ~(size_t)15;
+    a.off_le = (uint32_t)off;           off += (size_t)p->n_buckets * 8;
+    a.off_stash = (uint32_t)off;        off += (size_t)p->n_ticks * 3 * 8;
+    a.off_stash_valid = (uint32_t)off;  off += ((size_t)p->n_ticks + 7) & ~(size_t)7;
+    a.off_bits = (uint32_t)off;         off += (((size_t)p->n_ticks + 31) / 32) * 4;
+    off = (off + 7) & ~(size_t)7;
+    a.off_bar = (uint32_t)off;          off += 8;
+    if (off > (size_t)kMaxSmem)
+        return fail(CG_EINVAL, "geometry needs %zu bytes of shared memory per CTA (limit %d): "
+                    "(n_scalar+n_buckets)*row_pitch too large for the resident-tile kernel", off, kMaxSmem);
+    if ((size_t)(p->n_scalar + p->n_buckets) * p->row_pitch * esz >= (1u << 20))
+        return fail(CG_EINVAL, "tile exceeds the mbarrier transaction-count range");
+    a.smem_bytes = (uint32_t)off;
+    int threads = ((p->n_ticks + 31) / 32) * 32;
+    if (threads < 32) threads = 32;
+    if (threads > 512) threads = 512;
+    plan->block = threads;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess)
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per_sm = (int)(kMaxSmem / (off + 1024)) > 0 ? (int)(kMaxSmem / (off + 1024)) : 1;
+    int64_t g = (int64_t)sms * per_sm;
+    if (g > n_pairs) g = n_pairs;
+    if (g < 1) g = 1;
+    plan->grid = (int)g;
+    return CG_OK;
+}
+
+template <typename T>
+int launch_general(const GeneralPlan& plan, cudaStream_t s) {
+    auto kern = cg::general_kernel<T>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)plan.args.smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(general_kernel)");
+    kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch general_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
+// ---- standalone gate / replay kernels ------------------------------------------
+__global__ void gate_kernel(const double* __restrict__ new_m, const uint8_t* __restrict__ new_v,
+                            const double* __restrict__ old_m, const uint8_t* __restrict__ old_v,
+                            int64_t n, const __grid_constant__ cg_params p, uint8_t* __restrict__ detail) {
+    const int W = p.n_q + CG_M_EXTRA;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double* a = new_m + i * W;
+        const double* b = old_m + i * W;
+        const double nm[3] = {p.n_q > 0 ? a[p.gate_q] : NAN, a[p.n_q + CG_M_ERROR_RATE], a[p.n_q + CG_M_LATENCY_AVG]};
+        const double om[3] = {p.n_q > 0 ? b[p.gate_q] : NAN, b[p.n_q + CG_M_ERROR_RATE], b[p.n_q + CG_M_LATENCY_AVG]};
+        detail[i] = cg::gate_eval(nm, new_v[i], om, old_v[i], p);
+    }
+}
+
+__global__ void replay_kernel(const uint32_t* __restrict__ gate_bits, const uint8_t* __restrict__ has_previous,
+                              const int32_t* __restrict__ start_tick, int64_t n_pairs,
+                              const __grid_constant__ cg_params p, cg_decision* __restrict__ decisions) {
+    const int n_words = (p.n_ticks + 31) >> 5;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n_pairs; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t* bits = gate_bits + i * n_words;
+        const bool hp = has_previous ? has_previous[i] != 0 : true;
+        const int st = start_tick ? start_tick[i] : p.start_tick;
+        decisions[i] = cg::replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, hp, st, p);
+    }
+}
+
+int grid_for(int64_t n, int block) {
+    int64_t g = (n + block - 1) / block;
+    if (g > 148 * 16) g = 148 * 16;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+int run_general(const void* scalars, const void* buckets, const double* le, const int32_t* phase,
+                const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
+                const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
+                uint8_t* valid, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (n_pairs == 0) return CG_OK;
+    if (p->n_scalar > 0 && !scalars) return fail(CG_EINVAL, "scalars is NULL but n_scalar > 0");
+    if (p->n_buckets > 0 && (!buckets || !le)) return fail(CG_EINVAL, "buckets/le is NULL but n_buckets > 0");
+    if (!phase) return fail(CG_EINVAL, "phase is NULL");
+    if ((rc = check_aligned(scalars, "scalars"))) return rc;
+    if ((rc = check_aligned(buckets, "buckets"))) return rc;
+    GeneralPlan plan;
+    if ((rc = plan_general(p, n_pairs, &plan))) return rc;
+    cg::GeneralArgs& a = plan.args;
+    a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
+    a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
+    a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
+    cudaStream_t s = (cudaStream_t)stream;
+    return p->dtype == CG_F32 ? launch_general<float>(plan, s) : launch_general<double>(plan, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+int cg_abi_version(void) { return CG_ABI_VERSION; }
+const char* cg_last_error(void) { return g_err; }
+int64_t cg_launch_count(void) { return g_launches.load(); }
+
+int cg_params_default(cg_params* p) {
+    if (!p) return fail(CG_EINVAL, "params is NULL");
+    memset(p, 0, sizeof(*p));
+    p->struct_bytes = (int32_t)sizeof(cg_params);
+    p->dtype = CG_F64;
+    p->n_samples = 240; p->row_pitch = 240;
+    p->n_scalar = 4; p->n_buckets = 64;
+    p->scalar_role[0] = CG_ROLE_SERVER_TOTAL;
+    p->scalar_role[1] = CG_ROLE_SERVER_TOTAL | CG_ROLE_SERVER_ERROR;
+    p->scalar_role[2] = CG_ROLE_CLIENT_SUM;
+    p->scalar_role[3] = CG_ROLE_CLIENT_COUNT;
+    p->period_ms = 15000; p->window_ms = 60000;            // elapsed_time=60 (:363)
+    p->tick0_ms = 60000; p->tick_step_ms = 10000; p->n_ticks = 355;
+    p->left_open = 0;
+    p->n_q = 1; p->gate_q = 0; p->q[0] = 0.95;             // :367
+    p->one_plus_thr[0] = 1 + 0.05;                         // :176, :440
+    p->one_plus_thr[1] = 1 + 0.02;                         // :177, :447
+    p->one_plus_thr[2] = 1 + 0.05;                         // :178, :454
+    p->checks = CG_G_P95_OK | CG_G_ERR_OK | CG_G_AVG_OK;
+    p->init_current = 10; p->max_traffic = 100; p->step = 10;   // :187, :290-291
+    p->interval_ticks = 6; p->max_attempts = 10; p->attempt_delay_ticks = 1;   // :292-294
+    p->start_tick = 0;
+    return CG_OK;
+}
+
+int cg_params_check(const cg_params* p) { return check_params(p); }
+
+int cg_metric_width(const cg_params* p) { return p ? p->n_q + CG_M_EXTRA : -1; }
+
+int64_t cg_bytes_per_pair(const cg_params* p) {
+    if (!p) return -1;
+    return 2 * (int64_t)(p->n_scalar + p->n_buckets) * p->n_samples * (int64_t)elem_size(p) +
+           (int64_t)sizeof(cg_decision) + 8;
+}
+
+int cg_eval_grid(const void* scalars, const void* buckets, const double* le, const int32_t* phase,
+                 int64_t n_pairs, const cg_params* p, double* metrics, uint8_t* valid, void* stream) {
+    return run_general(scalars, buckets, le, phase, nullptr, nullptr, n_pairs, p, nullptr, nullptr,
+                       metrics, valid, stream);
+}
+
+int cg_eval_fused(const void* scalars, const void* buckets, const double* le, const int32_t* phase,
+                  const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
+                  const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
+                  uint8_t* valid, void* stream) {
+    if (n_pairs > 0 && !decisions) return fail(CG_EINVAL, "decisions is NULL");
+    return run_general(scalars, buckets, le, phase, has_previous, start_tick, n_pairs, p, decisions,
+                       gate_bits, metrics, valid, stream);
+}
+
+int cg_gate(const double* new_m, const uint8_t* new_v, const double* old_m, const uint8_t* old_v,
+            int64_t n, const cg_params* p, uint8_t* detail, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n < 0) return fail(CG_EINVAL, "n < 0");
+    if (n == 0) return CG_OK;
+    if (!new_m || !new_v || !old_m || !old_v || !detail) return fail(CG_EINVAL, "NULL argument");
+    gate_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(new_m, new_v, old_m, old_v, n, *p, detail);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch gate_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
+int cg_replay(const uint32_t* gate_bits, const uint8_t* has_previous, const int32_t* start_tick,
+              int64_t n_pairs, const cg_params* p, cg_decision* decisions, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (n_pairs == 0) return CG_OK;
+    if (!gate_bits || !decisions) return fail(CG_EINVAL, "NULL argument");
+    replay_kernel<<<grid_for(n_pairs, 128), 128, 0, (cudaStream_t)stream>>>(gate_bits, has_previous, start_tick,
+                                                                         n_pairs, *p, decisions);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch replay_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
+int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* block, int32_t* smem_bytes) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    GeneralPlan plan;
+    if ((rc = plan_general(p, n_pairs, &plan))) return rc;
+    if (grid) *grid = plan.grid;
+    if (block) *block = plan.block;
+    if (smem_bytes) *smem_bytes = (int32_t)plan.args.smem_bytes;
+    return CG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,152 @@
+// cg_math.cuh -- per-(series, tick) arithmetic of the canary path, device side.
+//
+// Everything here is IEEE fp64, one rounding per written operation (the library is
+// compiled with -fmad=false), in the same operation order as SURVEY.md Appendix A
+// (Prometheus 2.x extrapolatedRate / bucketQuantile) and as the reference's Python
+// (/root/reference/mlflow_operator.py:387-404, :440-454), so results are meant to be
+// bit-identical to the CPU restatement, not merely within 1e-6.
+#pragma once
+#include <stdint.h>
+#include <math.h>
+#include "../../include/canary_gate.h"
+
+namespace cg {
+
+#define CG_DEVINL __device__ __forceinline__
+
+CG_DEVINL int64_t floor_div(int64_t a, int64_t b) {
+    int64_t q = a / b, r = a % b;
+    return (r != 0 && ((r < 0) != (b < 0))) ? q - 1 : q;
+}
+CG_DEVINL int64_t ceil_div(int64_t a, int64_t b) { return -floor_div(-a, b); }
+
+// Window of a regular-grid series (sample i at phase + i*period) at one tick, plus the
+// extrapolation terms that depend only on timestamps (Appendix A step 3 and 5).
+struct TickGeom {
+    int    i0;        // first sample index in the window
+    int    n;         // samples in the window (< 2: the series yields no output)
+    double sampled;   // (ts_last - ts_first)/1000
+    double d_start;   // (ts_first - (t - r))/1000
+    double avg;       // sampled/(n-1)
+    double thr;       // avg*1.1
+    double end_term;  // d_end < thr ? d_end : avg/2
+};
+
+CG_DEVINL TickGeom tick_geom(const cg_params& p, int32_t phase, int tick) {
+    TickGeom g;
+    const int64_t t  = (int64_t)p.tick0_ms + (int64_t)tick * p.tick_step_ms;
+    const int64_t lo = t - p.window_ms;
+    int64_t a = p.left_open ? floor_div(lo - phase, p.period_ms) + 1
+                            : ceil_div(lo - phase, p.period_ms);
+    int64_t b = floor_div(t - phase, p.period_ms);
+    if (a < 0) a = 0;
+    if (b > p.n_samples - 1) b = p.n_samples - 1;
+    g.i0 = (int)a;
+    g.n  = (int)(b - a + 1);
+    if (g.n < 2) { g.n = g.n < 0 ? 0 : g.n; g.sampled = g.d_start = g.avg = g.thr = g.end_term = 0.0; return g; }
+    const int64_t first_t = (int64_t)phase + a * p.period_ms;
+    const int64_t last_t  = (int64_t)phase + b * p.period_ms;
+    g.d_start = (double)(first_t - lo) / 1000.0;
+    const double d_end = (double)(t - last_t) / 1000.0;
+    g.sampled = (double)(last_t - first_t) / 1000.0;
+    g.avg = g.sampled / (double)(g.n - 1);
+    g.thr = g.avg * 1.1;
+    g.end_term = (d_end < g.thr) ? d_end : g.avg / 2;
+    return g;
+}
+
+// Appendix A steps 4-6 for one series once `result` (step 2) is known.
+CG_DEVINL double extrapolate(double result, double first_v, const TickGeom& g) {
+    double d_start = g.d_start;
+    if (result > 0 && first_v >= 0) {
+        const double d_zero = g.sampled * (first_v / result);
+        if (d_zero < d_start) d_start = d_zero;
+    }
+    double ext = g.sampled;
+    ext += (d_start < g.thr) ? d_start : g.avg / 2;
+    ext += g.end_term;
+    return result * (ext / g.sampled);
+}
+
+// Appendix A step 2 over a window held in memory (`row` points at sample i0).
+template <typename T>
+CG_DEVINL double window_result(const T* __restrict__ row, int n, double& first_v) {
+    first_v = (double)row[0];
+    double result = (double)row[n - 1] - first_v;
+    double prev = first_v;
+    for (int i = 1; i < n; ++i) {
+        const double v = (double)row[i];
+        if (v < prev) result += prev;      // counter reset
+        prev = v;
+    }
+    return result;
+}
+
+template <typename T>
+CG_DEVINL double series_increase(const T* __restrict__ row, const TickGeom& g) {
+    double first_v;
+    const double result = window_result(row + g.i0, g.n, first_v);
+    return extrapolate(result, first_v, g);
+}
+
+// ---- should_promote_model (mlflow_operator.py:419-460) -------------------------
+// nm/om: [q_gate, error_rate, latency_avg] of the new / old version.
+CG_DEVINL uint8_t gate_eval(const double nm[3], uint8_t nv, const double om[3], uint8_t ov,
+                            const cg_params& p) {
+    const bool need_q = p.checks & CG_G_P95_OK, need_e = p.checks & CG_G_ERR_OK,
+               need_a = p.checks & CG_G_AVG_OK;
+    bool avail = true;                                               // :430-434
+    if (need_q && !((nv & CG_V_QUANTILE) && (ov & CG_V_QUANTILE))) avail = false;
+    if (need_e && !((nv & CG_V_ERROR_RATE) && (ov & CG_V_ERROR_RATE))) avail = false;
+    if (need_a && !((nv & CG_V_LATENCY_AVG) && (ov & CG_V_LATENCY_AVG))) avail = false;
+    if (!avail) return 0;
+    uint8_t d = CG_G_AVAILABLE;
+    bool promote = true;
+    if (need_q) { if (nm[0] <= om[0] * p.one_plus_thr[0]) d |= CG_G_P95_OK; else promote = false; }  // :440
+    if (need_e) { if (nm[1] <= om[1] * p.one_plus_thr[1]) d |= CG_G_ERR_OK; else promote = false; }  // :447
+    if (need_a) { if (nm[2] <= om[2] * p.one_plus_thr[2]) d |= CG_G_AVG_OK; else promote = false; }  // :454
+    if (promote) d |= CG_G_PROMOTE;                                  // :460
+    return d;
+}
+
+// ---- the traffic step loop (mlflow_operator.py:296-361) ------------------------
+template <typename BitFn>
+CG_DEVINL cg_decision replay_schedule(BitFn gate_bit, bool has_previous, int start_tick,
+                                      const cg_params& p) {
+    cg_decision d;
+    if (!has_previous) {                                             // :188-191, :289
+        d.traffic_current = p.max_traffic; d.traffic_prev = 0; d.state = CG_STATE_NO_CANARY;
+        d.n_promotions = 0; d.n_evals = 0; d.last_tick = -1;
+        return d;
+    }
+    int cur = p.init_current, prev = p.max_traffic - p.init_current; // :186-187
+    int tick = start_tick, n_prom = 0, n_eval = 0, last = -1;
+    int state = CG_STATE_IN_PROGRESS;
+    bool out_of_data = false;
+    while (cur < p.max_traffic && !out_of_data) {                    // :296
+        int attempt = 0;
+        bool success = false;
+        while (attempt < p.max_attempts) {                           // :300
+            if (tick >= p.n_ticks || tick < 0) { out_of_data = true; break; }
+            ++n_eval; last = tick;
+            if (gate_bit(tick)) {                                    // :310
+                cur += p.step; prev -= p.step;                       // :312-313
+                if (cur > p.max_traffic) cur = p.max_traffic;        // :316
+                if (prev < 0) prev = 0;                              // :317
+                ++n_prom; success = true;
+                break;
+            }
+            ++attempt;                                               // :337
+            if (attempt < p.max_attempts) tick += p.attempt_delay_ticks;   // :340
+        }
+        if (out_of_data) break;
+        if (!success) { state = CG_STATE_ABORTED; break; }           // :347-349
+        tick += p.interval_ticks;                                    // :352
+    }
+    if (cur == p.max_traffic) state = CG_STATE_COMPLETE;             // :355
+    d.traffic_current = cur; d.traffic_prev = prev; d.state = state;
+    d.n_promotions = n_prom; d.n_evals = n_eval; d.last_tick = last;
+    return d;
+}
+
+}  // namespace cg

@@ -1,0 +1,128 @@
+"""Batched device API: torch tensors in, torch tensors out, every FLOP in
+libcanarygate.so.  torch is plumbing here (device memory, streams), not compute."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from .params import CG_F32, CgParams
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _want(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (no CPU fallback in this library)")
+    if t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+def _elem_dtype(p: CgParams):
+    return torch.float32 if p.dtype == CG_F32 else torch.float64
+
+
+def _check_series(scalars, buckets, le, phase, p: CgParams) -> int:
+    n = phase.shape[0]
+    _want(phase, torch.int32, "phase")
+    if tuple(phase.shape) != (n, 2):
+        raise ValueError("phase must be [n_pairs, 2]")
+    dt = _elem_dtype(p)
+    if p.n_scalar:
+        _want(scalars, dt, "scalars")
+        if tuple(scalars.shape) != (n, 2, p.n_scalar, p.row_pitch):
+            raise ValueError(f"scalars must be [{n}, 2, {p.n_scalar}, {p.row_pitch}], got {tuple(scalars.shape)}")
+    if p.n_buckets:
+        _want(buckets, dt, "buckets")
+        if tuple(buckets.shape) != (n, 2, p.n_buckets, p.row_pitch):
+            raise ValueError(f"buckets must be [{n}, 2, {p.n_buckets}, {p.row_pitch}], got {tuple(buckets.shape)}")
+        _want(le, torch.float64, "le")
+        if le.numel() != p.n_buckets:
+            raise ValueError("le must have n_buckets entries")
+    return n
+
+
+def eval_grid(scalars, buckets, le, phase, p: CgParams) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Batched get_model_metrics (mlflow_operator.py:363-417) on the dense tick grid.
+    -> metrics [N, 2, n_ticks, n_q+5] fp64, valid [N, 2, n_ticks] uint8."""
+    n = _check_series(scalars, buckets, le, phase, p)
+    metrics = torch.empty((n, 2, p.n_ticks, p.metric_width), dtype=torch.float64, device=phase.device)
+    valid = torch.empty((n, 2, p.n_ticks), dtype=torch.uint8, device=phase.device)
+    _lib.check(_lib.lib.cg_eval_grid(_ptr(scalars if p.n_scalar else None), _ptr(buckets if p.n_buckets else None),
+                                     _ptr(le if p.n_buckets else None), _ptr(phase), n, C.byref(p),
+                                     _ptr(metrics), _ptr(valid), _stream_ptr()), "cg_eval_grid")
+    return metrics, valid
+
+
+def gate(new_m, new_v, old_m, old_v, p: CgParams) -> torch.Tensor:
+    """Batched should_promote_model (mlflow_operator.py:419-460) -> detail bytes."""
+    n = new_v.numel()
+    for t, dt, nm in ((new_m, torch.float64, "new_m"), (old_m, torch.float64, "old_m"),
+                      (new_v, torch.uint8, "new_v"), (old_v, torch.uint8, "old_v")):
+        _want(t, dt, nm)
+    if new_m.numel() != n * p.metric_width or old_m.numel() != n * p.metric_width:
+        raise ValueError("metric records must be [n, n_q+5]")
+    detail = torch.empty(n, dtype=torch.uint8, device=new_m.device)
+    _lib.check(_lib.lib.cg_gate(_ptr(new_m), _ptr(new_v), _ptr(old_m), _ptr(old_v), n, C.byref(p),
+                                _ptr(detail), _stream_ptr()), "cg_gate")
+    return detail
+
+
+def replay(gate_bits, p: CgParams, has_previous=None, start_tick=None, out=None) -> torch.Tensor:
+    """The traffic step loop (mlflow_operator.py:296-361) over gate bit-vectors
+    -> decisions [N, 6] int32 (cur, prev, state, n_promotions, n_evals, last_tick)."""
+    _want(gate_bits, torch.int32, "gate_bits")
+    n = gate_bits.shape[0]
+    if gate_bits.shape[1] != p.n_words:
+        raise ValueError("gate_bits must be [n_pairs, ceil(n_ticks/32)] int32")
+    if has_previous is not None:
+        _want(has_previous, torch.uint8, "has_previous")
+    if start_tick is not None:
+        _want(start_tick, torch.int32, "start_tick")
+    dec = out if out is not None else torch.empty((n, 6), dtype=torch.int32, device=gate_bits.device)
+    _want(dec, torch.int32, "decisions")
+    _lib.check(_lib.lib.cg_replay(_ptr(gate_bits), _ptr(has_previous), _ptr(start_tick), n, C.byref(p),
+                                  _ptr(dec), _stream_ptr()), "cg_replay")
+    return dec
+
+
+def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, start_tick=None,
+               want_bits: bool = False, want_metrics: bool = False, out=None):
+    """metrics -> gate -> step loop in one pass over the series (mlflow_operator.py:302-317
+    for every MlflowModel at once).  -> decisions [N, 6] int32 (+ gate_bits, metrics, valid)."""
+    n = _check_series(scalars, buckets, le, phase, p)
+    dev = phase.device
+    if has_previous is not None:
+        _want(has_previous, torch.uint8, "has_previous")
+    if start_tick is not None:
+        _want(start_tick, torch.int32, "start_tick")
+    dec = out if out is not None else torch.empty((n, 6), dtype=torch.int32, device=dev)
+    _want(dec, torch.int32, "decisions")
+    if dec.numel() < n * 6:
+        raise ValueError("decisions buffer too small")
+    bits = torch.empty((n, p.n_words), dtype=torch.int32, device=dev) if want_bits else None
+    metrics = valid = None
+    if want_metrics:
+        metrics = torch.empty((n, 2, p.n_ticks, p.metric_width), dtype=torch.float64, device=dev)
+        valid = torch.empty((n, 2, p.n_ticks), dtype=torch.uint8, device=dev)
+    _lib.check(_lib.lib.cg_eval_fused(_ptr(scalars if p.n_scalar else None), _ptr(buckets if p.n_buckets else None),
+                                      _ptr(le if p.n_buckets else None), _ptr(phase), _ptr(has_previous),
+                                      _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits), _ptr(metrics),
+                                      _ptr(valid), _stream_ptr()), "cg_eval_fused")
+    res = [dec]
+    if want_bits:
+        res.append(bits)
+    if want_metrics:
+        res += [metrics, valid]
+    return res[0] if len(res) == 1 else tuple(res)
