@@ -184,6 +184,13 @@ int cg_eval_fused(const void* scalars, const void* buckets, const double* le,
                   cg_decision* decisions, uint32_t* gate_bits,
                   double* metrics, uint8_t* valid, void* stream);
 
+/* Benchmark / test utility with no counterpart in the reference: fill device arrays with
+ * seeded synthetic series (SURVEY.md 8(d) model).  Values are a pure function of
+ * (seed, pair_offset + local pair, version, series, sample), so shards agree. */
+int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase,
+                  int64_t n_pairs, int64_t pair_offset, const cg_params* p, uint64_t seed,
+                  double reset_prob, double adversarial, void* stream);
+
 /* Launch geometry the library would use (for reporting): CTAs, threads, dynamic smem. */
 int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* block,
                    int32_t* smem_bytes);

@@ -9,6 +9,7 @@
 
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
+#include "cg_synth.cuh"
 
 namespace {
 
@@ -257,6 +258,31 @@ int cg_replay(const uint32_t* gate_bits, const uint8_t* has_previous, const int3
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "launch replay_kernel");
     g_launches.fetch_add(1);
+    return CG_OK;
+}
+
+int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase, int64_t n_pairs,
+                  int64_t pair_offset, const cg_params* p, uint64_t seed, double reset_prob,
+                  double adversarial, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (n_pairs == 0) return CG_OK;
+    if (!phase || (p->n_scalar && !scalars) || (p->n_buckets && (!buckets || !le)))
+        return fail(CG_EINVAL, "NULL argument");
+    cg::SynthArgs a;
+    a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase; a.n_pairs = n_pairs;
+    a.pair_offset = pair_offset; a.seed = seed; a.reset_prob = reset_prob; a.adversarial = adversarial;
+    int g = p->period_ms, h = p->tick_step_ms;
+    while (h) { int t = g % h; g = h; h = t; }
+    a.phase_avoid = g;
+    a.p = *p;
+    const int64_t total = n_pairs * 2 * (p->n_scalar + p->n_buckets);
+    const int grid = grid_for(total, 128);
+    if (p->dtype == CG_F32) cg::synth_kernel<float><<<grid, 128, 0, (cudaStream_t)stream>>>(a);
+    else cg::synth_kernel<double><<<grid, 128, 0, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch synth_kernel");
     return CG_OK;
 }
 

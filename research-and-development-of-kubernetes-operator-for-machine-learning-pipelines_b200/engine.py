@@ -126,3 +126,76 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
     if want_metrics:
         res += [metrics, valid]
     return res[0] if len(res) == 1 else tuple(res)
+
+
+def synth_fill(n_pairs: int, p: CgParams, le: torch.Tensor, seed: int = 0xC0FFEE, pair_offset: int = 0,
+               reset_prob: float = 1.0 / 240.0, adversarial: float = 0.01, device=None):
+    """Allocate and fill device series with the library's seeded generator kernel
+    (benchmark / test utility).  -> scalars, buckets, phase."""
+    dev = le.device if device is None else torch.device(device)
+    dt = _elem_dtype(p)
+    scalars = torch.empty((n_pairs, 2, p.n_scalar, p.row_pitch), dtype=dt, device=dev)
+    buckets = torch.empty((n_pairs, 2, p.n_buckets, p.row_pitch), dtype=dt, device=dev)
+    phase = torch.empty((n_pairs, 2), dtype=torch.int32, device=dev)
+    _lib.check(_lib.lib.cg_synth_fill(_ptr(scalars), _ptr(buckets), _ptr(le), _ptr(phase), n_pairs, pair_offset,
+                                      C.byref(p), seed, reset_prob, adversarial, _stream_ptr()), "cg_synth_fill")
+    return scalars, buckets, phase
+
+
+class HostPipeline:
+    """End-to-end path for HOST-resident series (what an ingest layer hands over): pinned
+    host arrays are streamed to the GPU in chunks of pairs on a copy stream while the
+    previous chunk is evaluated on a compute stream; decision records come back to pinned
+    host memory.  Staging buffers are allocated once here and reused by every `run`."""
+
+    def __init__(self, p: CgParams, chunk_pairs: int = 4096, device=None):
+        self.p = p
+        self.chunk = int(chunk_pairs)
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        dt = _elem_dtype(p)
+        mk = lambda *s, d=dt: torch.empty(s, dtype=d, device=self.dev)  # noqa: E731
+        self.slots = [dict(scalars=mk(self.chunk, 2, p.n_scalar, p.row_pitch),
+                           buckets=mk(self.chunk, 2, p.n_buckets, p.row_pitch),
+                           phase=mk(self.chunk, 2, d=torch.int32),
+                           dec=mk(self.chunk, 6, d=torch.int32),
+                           copied=torch.cuda.Event(), done=torch.cuda.Event()) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=self.dev)
+        self.compute_stream = torch.cuda.Stream(device=self.dev)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run(self, scalars_h, buckets_h, phase_h, le_dev, out_h=None):
+        """scalars_h/buckets_h/phase_h: pinned CPU tensors in the library layout.
+        -> decisions [N, 6] int32 in pinned host memory (synchronised on return)."""
+        p = self.p
+        n = phase_h.shape[0]
+        for t, nm in ((scalars_h, "scalars_h"), (buckets_h, "buckets_h"), (phase_h, "phase_h")):
+            if t.is_cuda or not t.is_contiguous():
+                raise ValueError(f"{nm} must be a contiguous CPU tensor")
+        if out_h is None:
+            out_h = torch.empty((n, 6), dtype=torch.int32, pin_memory=True)
+        self.h2d_bytes = self.d2h_bytes = 0
+        cur = torch.cuda.current_stream(self.dev)
+        self.copy_stream.wait_stream(cur)
+        self.compute_stream.wait_stream(cur)
+        for c, lo in enumerate(range(0, n, self.chunk)):
+            hi = min(lo + self.chunk, n)
+            m = hi - lo
+            s = self.slots[c & 1]
+            with torch.cuda.stream(self.copy_stream):
+                if c >= 2:
+                    self.copy_stream.wait_event(s["done"])      # slot free again
+                s["scalars"][:m].copy_(scalars_h[lo:hi], non_blocking=True)
+                s["buckets"][:m].copy_(buckets_h[lo:hi], non_blocking=True)
+                s["phase"][:m].copy_(phase_h[lo:hi], non_blocking=True)
+                s["copied"].record(self.copy_stream)
+            self.h2d_bytes += sum(x[lo:hi].numel() * x.element_size() for x in (scalars_h, buckets_h, phase_h))
+            with torch.cuda.stream(self.compute_stream):
+                self.compute_stream.wait_event(s["copied"])
+                eval_fused(s["scalars"][:m], s["buckets"][:m], le_dev, s["phase"][:m], p, out=s["dec"][:m])
+                out_h[lo:hi].copy_(s["dec"][:m], non_blocking=True)
+                s["done"].record(self.compute_stream)
+            self.d2h_bytes += m * 24
+        cur.wait_stream(self.compute_stream)
+        self.compute_stream.synchronize()
+        return out_h

@@ -201,3 +201,39 @@ def test_properties_at_scale():
                            b.le, np.ascontiguousarray(big.phase[idx]), p)
     want, wbits = co.eval_fused(sub.scalars, sub.buckets, sub.le, sub.phase, p, n_threads=8)
     assert np.array_equal(dec[idx], want) and np.array_equal(bits[idx], wbits)
+
+
+def test_device_generated_series_match_oracle():
+    """The benchmark's on-device generator (cg_synth_fill): whatever it writes, the CUDA
+    path and the oracle must agree on it; and shards must be consistent."""
+    p = P.make_params()
+    le = torch.from_numpy(synth.default_le(p.n_buckets)).cuda()
+    sc, bk, ph = engine.synth_fill(192, p, le, seed=77, adversarial=0.1)
+    sc2, bk2, ph2 = engine.synth_fill(64, p, le, seed=77, pair_offset=128, adversarial=0.1)
+    assert torch.equal(sc[128:], sc2) and torch.equal(bk[128:], bk2) and torch.equal(ph[128:], ph2)
+    dec, bits = engine.eval_fused(sc, bk, le, ph, p, want_bits=True)
+    m, v = engine.eval_grid(sc, bk, le, ph, p)
+    h = [t.cpu().numpy() for t in (sc, bk, ph)]
+    want_m, want_v = co.eval_grid(h[0], h[1], le.cpu().numpy(), h[2], p, n_threads=8)
+    assert_metrics_match(m.cpu().numpy(), want_m, v.cpu().numpy(), want_v, what="synth")
+    want, wbits = co.eval_fused(h[0], h[1], le.cpu().numpy(), h[2], p, n_threads=8)
+    assert np.array_equal(dec.cpu().numpy(), want)
+    assert np.array_equal(bits.cpu().numpy().view(np.uint32), wbits)
+    states = np.bincount(want[:, 2], minlength=4)
+    assert states[P.STATE_COMPLETE] > 0 and states[P.STATE_ABORTED] > 0   # both outcomes occur
+    # counters really do reset in this workload
+    assert (np.diff(h[1][:, :, :, :p.n_samples], axis=-1) < 0).any()
+
+
+def test_host_pipeline_matches_device_path():
+    p = P.make_params(n_samples=120, n_buckets=16)
+    b = synth.generate(p, 300, seed=31)
+    want, _ = gpu_fused(b)
+    pipe = engine.HostPipeline(p, chunk_pairs=64)
+    le = torch.from_numpy(b.le).cuda()
+    pin = lambda a: torch.from_numpy(a).pin_memory()  # noqa: E731
+    for _ in range(2):
+        out = pipe.run(pin(b.scalars), pin(b.buckets), pin(b.phase), le)
+        assert np.array_equal(out.numpy(), want)
+    assert pipe.h2d_bytes == b.scalars.nbytes + b.buckets.nbytes + b.phase.nbytes
+    assert pipe.d2h_bytes == 300 * 24
