@@ -191,6 +191,18 @@ int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase
                   int64_t n_pairs, int64_t pair_offset, const cg_params* p, uint64_t seed,
                   double reset_prob, double adversarial, void* stream);
 
+/* Same as cg_eval_fused with an explicit kernel choice: path 0 = automatic, 1 = the general
+ * resident-tile kernel, 2 = the streaming kernel (CG_EINVAL if the geometry is not covered:
+ * it needs window = 4 scrape periods and tick step = 2/3 period, the reference's constants
+ * (:363, :294) with 15 s scrapes).  Both kernels give bit-identical results. */
+int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const double* le,
+                       const int32_t* phase, const uint8_t* has_previous, const int32_t* start_tick,
+                       int64_t n_pairs, const cg_params* p, cg_decision* decisions,
+                       uint32_t* gate_bits, double* metrics, uint8_t* valid, void* stream);
+
+/* 1 if cg_eval_fused would take the streaming kernel for these params, else 0. */
+int cg_stream_eligible(const cg_params* p);
+
 /* Launch geometry the library would use (for reporting): CTAs, threads, dynamic smem. */
 int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* block,
                    int32_t* smem_bytes);

@@ -3,25 +3,36 @@
 nvcc cross-compiles here without a GPU; the .so is git-ignored but travels to the
 GPU box with the gpurun snapshot.  -fmad=false: the reference computes in Python
 floats, one IEEE rounding per operation, so no multiply-add may be contracted.
+The streaming kernel is instantiated per (element type, quantile count) in separate
+translation units that compile in parallel.
 """
 from __future__ import annotations
 
 import os
 import shutil
 import subprocess
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
+OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcanarygate.so")
-SOURCES = ["cg_api.cu"]
-HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_stream.cuh", "cg_synth.cuh"]
+HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_stream.cuh", "cg_synth.cuh",
+           os.path.join(ROOT, "include", "canary_gate.h")]
 
-NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-fmad=false", "--shared", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default",
-    "-Xptxas", "-v", "-cudart", "shared",
-]
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+CFLAGS = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-fmad=false", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+
+
+def _units():
+    units = [("cg_api", "cg_api.cu", [])]
+    for tname, tchar in (("double", "d"), ("float", "f")):
+        for nq in (1, 2, 3, 4):
+            name = f"cg_launch_stream_{tchar}{nq}"
+            units.append((name, "cg_stream_inst.cu",
+                          [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]))
+    return units
 
 
 def _nvcc() -> str:
@@ -31,29 +42,58 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found: libcanarygate.so cannot be built")
 
 
+def _newest_dep(src: str) -> float:
+    deps = [os.path.join(CSRC, src)] + [h if os.path.isabs(h) else os.path.join(CSRC, h) for h in HEADERS]
+    deps.append(os.path.abspath(__file__))
+    return max(os.path.getmtime(d) for d in deps if os.path.exists(d))
+
+
 def stale() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
-    deps.append(os.path.join(ROOT, "include", "canary_gate.h"))
-    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+    return any(_newest_dep(src) > t for _, src, _ in _units())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    nvcc = _nvcc()
+    os.makedirs(OBJ, exist_ok=True)
+    log_path = os.path.join(HERE, "build.log")
+    logs = []
+
+    def compile_one(unit):
+        name, src, defs = unit
+        obj = os.path.join(OBJ, name + ".o")
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) >= _newest_dep(src):
+            return obj, 0, ""
+        cmd = [nvcc] + CFLAGS + defs + ["-c", os.path.join(CSRC, src), "-o", obj]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        return obj, res.returncode, " ".join(cmd) + "\n" + res.stdout + res.stderr
+
+    with ThreadPoolExecutor(max_workers=min(9, os.cpu_count() or 1)) as ex:
+        results = list(ex.map(compile_one, _units()))
+    objs = []
+    for obj, rc, log in results:
+        logs.append(log)
+        if rc != 0:
+            with open(log_path, "w") as f:
+                f.write("\n".join(logs))
+            raise RuntimeError("nvcc failed:\n" + log)
+        objs.append(obj)
+    cmd = [nvcc] + ARCH + ["--shared", "-cudart", "shared", "-o", LIB] + objs
     res = subprocess.run(cmd, capture_output=True, text=True)
-    log = os.path.join(HERE, "build.log")
-    with open(log, "w") as f:
-        f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
+    logs.append(" ".join(cmd) + "\n" + res.stdout + res.stderr)
+    with open(log_path, "w") as f:
+        f.write("\n".join(logs))
     if verbose:
-        print(res.stdout + res.stderr)
+        print("\n".join(logs))
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+        raise RuntimeError("link failed:\n" + res.stdout + res.stderr)
     return LIB
 
 
 if __name__ == "__main__":
-    print(build(force=True, verbose=True))
+    import sys
+    print(build(force="--force" in sys.argv, verbose=True))

@@ -9,6 +9,7 @@
 
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
+#include "cg_stream.cuh"
 #include "cg_synth.cuh"
 
 namespace {
@@ -118,6 +119,87 @@ int launch_general(const GeneralPlan& plan, cudaStream_t s) {
     return CG_OK;
 }
 
+// ---- streaming kernel: eligibility, shared-memory plan, launch ----------------------
+struct StreamPlan {
+    cg::StreamArgs args;
+    int grid, block, cw_template;
+};
+
+bool stream_eligible(const cg_params* p) {
+    if ((int64_t)p->window_ms != 4 * (int64_t)p->period_ms) return false;
+    if (3 * (int64_t)p->tick_step_ms != 2 * (int64_t)p->period_ms) return false;
+    if (p->n_scalar + p->n_buckets == 0 || p->n_ticks < 1) return false;
+    if (p->n_samples < 4) return false;
+    const int groups = (p->n_ticks + cg::kG - 1) / cg::kG;
+    if (groups > 15 * 32) return false;
+    const size_t slot = (size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p);
+    if (slot >= (1u << 20)) return false;
+    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * (((size_t)p->n_ticks + 31) / 32) * 4 + 2 * 32 * 8 + 256;
+    return 3 * slot + fixed <= (size_t)kMaxSmem;
+}
+
+int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
+    cg::StreamArgs& a = plan->args;
+    memset(&a, 0, sizeof(a));
+    a.p = *p;
+    a.n_pairs = n_pairs;
+    a.n_groups = (p->n_ticks + cg::kG - 1) / cg::kG;
+    a.consumer_warps = (a.n_groups + 31) / 32;
+    plan->cw_template = a.consumer_warps <= 4 ? 4 : 15;
+    a.slot_bytes = (uint32_t)((size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p));
+    const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
+    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * n_words * 4 + 2 * 32 * 8 + 256;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
+    const int threads = a.consumer_warps * 32 + 32;
+    int per_sm = 1, slots = 0;
+    for (int c = (a.consumer_warps <= 4 ? 3 : 1); c >= 1; --c) {
+        if (c * threads > 2048) continue;
+        const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
+        if (budget <= fixed) continue;
+        const int sl = (int)((budget - fixed) / a.slot_bytes);
+        if (sl >= 6 || (c == 1 && sl >= 3)) { per_sm = c; slots = sl; break; }
+        if (sl >= 3 && slots == 0) { per_sm = c; slots = sl; }
+    }
+    if (slots < 3) return fail(CG_EINVAL, "streaming kernel: ring does not fit shared memory");
+    if (slots > 32) slots = 32;
+    a.n_slots = slots;
+    size_t off = (size_t)slots * a.slot_bytes;
+    a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
+    a.off_bits = (uint32_t)off; off += 3 * n_words * 4;
+    off = (off + 7) & ~(size_t)7;
+    a.off_bars = (uint32_t)off; off += (size_t)2 * slots * 8;
+    a.smem_bytes = (uint32_t)off;
+    plan->block = threads;
+    int64_t g = (int64_t)sms * per_sm;
+    if (g > n_pairs) g = n_pairs;
+    if (g < 1) g = 1;
+    plan->grid = (int)g;
+    return CG_OK;
+}
+
+}  // namespace
+// one per translation unit cg_stream_inst.cu (see build.py)
+#define CG_DECL_INST(n) cudaError_t n(const cg::StreamArgs&, int, int, int, cudaStream_t)
+CG_DECL_INST(cg_launch_stream_d1); CG_DECL_INST(cg_launch_stream_d2); CG_DECL_INST(cg_launch_stream_d3);
+CG_DECL_INST(cg_launch_stream_d4); CG_DECL_INST(cg_launch_stream_f1); CG_DECL_INST(cg_launch_stream_f2);
+CG_DECL_INST(cg_launch_stream_f3); CG_DECL_INST(cg_launch_stream_f4);
+namespace {
+
+int launch_stream(const StreamPlan& plan, cudaStream_t s) {
+    typedef cudaError_t (*fn_t)(const cg::StreamArgs&, int, int, int, cudaStream_t);
+    static const fn_t table[2][4] = {
+        {cg_launch_stream_d1, cg_launch_stream_d2, cg_launch_stream_d3, cg_launch_stream_d4},
+        {cg_launch_stream_f1, cg_launch_stream_f2, cg_launch_stream_f3, cg_launch_stream_f4}};
+    int nq = plan.args.p.n_q < 1 ? 1 : plan.args.p.n_q;
+    const cudaError_t e = table[plan.args.p.dtype == CG_F32 ? 1 : 0][nq - 1](plan.args, plan.grid, plan.block,
+                                                                           plan.cw_template, s);
+    if (e != cudaSuccess) return cuda_fail(e, "launch stream_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
 // ---- standalone gate / replay kernels ------------------------------------------
 __global__ void gate_kernel(const double* __restrict__ new_m, const uint8_t* __restrict__ new_v,
                             const double* __restrict__ old_m, const uint8_t* __restrict__ old_v,
@@ -154,7 +236,7 @@ int grid_for(int64_t n, int block) {
 int run_general(const void* scalars, const void* buckets, const double* le, const int32_t* phase,
                 const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
                 const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
-                uint8_t* valid, void* stream) {
+                uint8_t* valid, void* stream, int path = 0) {
     int rc = check_params(p);
     if (rc) return rc;
     if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
@@ -164,13 +246,23 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     if (!phase) return fail(CG_EINVAL, "phase is NULL");
     if ((rc = check_aligned(scalars, "scalars"))) return rc;
     if ((rc = check_aligned(buckets, "buckets"))) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (decisions && path != 1 && stream_eligible(p)) {
+        StreamPlan sp;
+        if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
+        cg::StreamArgs& a = sp.args;
+        a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
+        a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
+        a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
+        return launch_stream(sp, s);
+    }
+    if (path == 2) return fail(CG_EINVAL, "geometry not covered by the streaming kernel");
     GeneralPlan plan;
     if ((rc = plan_general(p, n_pairs, &plan))) return rc;
     cg::GeneralArgs& a = plan.args;
     a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
     a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
     a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
-    cudaStream_t s = (cudaStream_t)stream;
     return p->dtype == CG_F32 ? launch_general<float>(plan, s) : launch_general<double>(plan, s);
 }
 
@@ -232,6 +324,21 @@ int cg_eval_fused(const void* scalars, const void* buckets, const double* le, co
                        gate_bits, metrics, valid, stream);
 }
 
+int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const double* le,
+                       const int32_t* phase, const uint8_t* has_previous, const int32_t* start_tick,
+                       int64_t n_pairs, const cg_params* p, cg_decision* decisions, uint32_t* gate_bits,
+                       double* metrics, uint8_t* valid, void* stream) {
+    if (n_pairs > 0 && !decisions) return fail(CG_EINVAL, "decisions is NULL");
+    if (path < 0 || path > 2) return fail(CG_EINVAL, "path must be 0 (auto), 1 (general) or 2 (streaming)");
+    return run_general(scalars, buckets, le, phase, has_previous, start_tick, n_pairs, p, decisions,
+                       gate_bits, metrics, valid, stream, path);
+}
+
+int cg_stream_eligible(const cg_params* p) {
+    if (check_params(p)) return 0;
+    return stream_eligible(p) ? 1 : 0;
+}
+
 int cg_gate(const double* new_m, const uint8_t* new_v, const double* old_m, const uint8_t* old_v,
             int64_t n, const cg_params* p, uint8_t* detail, void* stream) {
     int rc = check_params(p);
@@ -289,6 +396,14 @@ int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase
 int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* block, int32_t* smem_bytes) {
     int rc = check_params(p);
     if (rc) return rc;
+    if (stream_eligible(p)) {
+        StreamPlan sp;
+        if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
+        if (grid) *grid = sp.grid;
+        if (block) *block = sp.block;
+        if (smem_bytes) *smem_bytes = (int32_t)sp.args.smem_bytes;
+        return CG_OK;
+    }
     GeneralPlan plan;
     if ((rc = plan_general(p, n_pairs, &plan))) return rc;
     if (grid) *grid = plan.grid;

@@ -1,0 +1,9 @@
+// cg_stream_inst.cu -- one translation unit per (element type, quantile count) instance of the
+// streaming kernel, so the instances compile in parallel.  Built with
+//   -DCG_INST_T=double|float -DCG_INST_NQ=1..4 -DCG_INST_NAME=cg_launch_stream_<d|f><nq>
+#include <cuda_runtime.h>
+#include "cg_stream.cuh"
+
+cudaError_t CG_INST_NAME(const cg::StreamArgs& a, int grid, int block, int cw_template, cudaStream_t s) {
+    return cg::launch_stream_tn<CG_INST_T, CG_INST_NQ>(a, grid, block, cw_template, s);
+}

@@ -98,9 +98,10 @@ def replay(gate_bits, p: CgParams, has_previous=None, start_tick=None, out=None)
 
 
 def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, start_tick=None,
-               want_bits: bool = False, want_metrics: bool = False, out=None):
+               want_bits: bool = False, want_metrics: bool = False, out=None, path: int = 0):
     """metrics -> gate -> step loop in one pass over the series (mlflow_operator.py:302-317
-    for every MlflowModel at once).  -> decisions [N, 6] int32 (+ gate_bits, metrics, valid)."""
+    for every MlflowModel at once).  -> decisions [N, 6] int32 (+ gate_bits, metrics, valid).
+    path: 0 = let the library choose, 1 = general kernel, 2 = streaming kernel."""
     n = _check_series(scalars, buckets, le, phase, p)
     dev = phase.device
     if has_previous is not None:
@@ -116,16 +117,22 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
     if want_metrics:
         metrics = torch.empty((n, 2, p.n_ticks, p.metric_width), dtype=torch.float64, device=dev)
         valid = torch.empty((n, 2, p.n_ticks), dtype=torch.uint8, device=dev)
-    _lib.check(_lib.lib.cg_eval_fused(_ptr(scalars if p.n_scalar else None), _ptr(buckets if p.n_buckets else None),
-                                      _ptr(le if p.n_buckets else None), _ptr(phase), _ptr(has_previous),
-                                      _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits), _ptr(metrics),
-                                      _ptr(valid), _stream_ptr()), "cg_eval_fused")
+    _lib.check(_lib.lib.cg_eval_fused_path(path, _ptr(scalars if p.n_scalar else None),
+                                           _ptr(buckets if p.n_buckets else None),
+                                           _ptr(le if p.n_buckets else None), _ptr(phase), _ptr(has_previous),
+                                           _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits), _ptr(metrics),
+                                           _ptr(valid), _stream_ptr()), "cg_eval_fused")
     res = [dec]
     if want_bits:
         res.append(bits)
     if want_metrics:
         res += [metrics, valid]
     return res[0] if len(res) == 1 else tuple(res)
+
+
+def stream_eligible(p: CgParams) -> bool:
+    """True if cg_eval_fused takes the streaming kernel for these params."""
+    return bool(_lib.lib.cg_stream_eligible(C.byref(p)))
 
 
 def synth_fill(n_pairs: int, p: CgParams, le: torch.Tensor, seed: int = 0xC0FFEE, pair_offset: int = 0,

@@ -18,12 +18,21 @@ def gpu_grid(batch):
     return m.cpu().numpy(), v.cpu().numpy()
 
 
-def gpu_fused(batch, has_previous=None, start_tick=None, want_bits=True):
+def gpu_fused_metrics(batch, path=0):
+    """decisions, bits, metrics, valid from ONE fused launch (path 2 = streaming kernel)."""
+    st = upload(batch)
+    dec, bits, m, v = engine.eval_fused(st.scalars, st.buckets, st.le, st.phase, batch.params,
+                                        want_bits=True, want_metrics=True, path=path)
+    torch.cuda.synchronize()
+    return dec.cpu().numpy(), bits.cpu().numpy().view(np.uint32), m.cpu().numpy(), v.cpu().numpy()
+
+
+def gpu_fused(batch, has_previous=None, start_tick=None, want_bits=True, path=0):
     st = upload(batch)
     hp = None if has_previous is None else torch.from_numpy(has_previous).cuda()
     stt = None if start_tick is None else torch.from_numpy(start_tick).cuda()
     out = engine.eval_fused(st.scalars, st.buckets, st.le, st.phase, batch.params,
-                            has_previous=hp, start_tick=stt, want_bits=want_bits)
+                            has_previous=hp, start_tick=stt, want_bits=want_bits, path=path)
     torch.cuda.synchronize()
     if want_bits:
         return out[0].cpu().numpy(), out[1].cpu().numpy().view(np.uint32)

@@ -10,7 +10,7 @@ import torch
 import canary_b200  # noqa: F401
 from canary_b200 import engine, params as P, synth
 from golden_util import fdec, golden_record, load_canary_batches, load_json, records_equal
-from gpu_util import assert_metrics_match, gpu_fused, gpu_grid
+from gpu_util import assert_metrics_match, gpu_fused, gpu_fused_metrics, gpu_grid
 from oracle import c_oracle as co
 
 pytestmark = pytest.mark.gpu
@@ -114,6 +114,11 @@ CONFIGS = {
 }
 
 
+# geometries the streaming kernel covers (window = 4 periods, tick step = 2/3 period)
+STREAMING = {"cfg2_error_rate_only", "cfg3_quantiles", "cfg4_full_resets", "k5_feedback_b12",
+             "left_open_coincident", "closed_coincident", "ragged_pitch", "short_series"}
+
+
 @pytest.mark.parametrize("name", sorted(CONFIGS))
 def test_seeded_batch_matches_oracle(name):
     cfg = CONFIGS[name]
@@ -123,9 +128,13 @@ def test_seeded_batch_matches_oracle(name):
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what=name)
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    got_dec, got_bits = gpu_fused(b)
-    assert np.array_equal(got_bits, want_bits), f"{name}: gate bits differ"
-    assert np.array_equal(got_dec, want_dec), f"{name}: decisions differ"
+    paths = [1, 2] if engine.stream_eligible(p) else [1]
+    assert engine.stream_eligible(p) == (name in STREAMING), name
+    for path in paths:
+        got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
+        assert np.array_equal(got_bits, want_bits), f"{name} path {path}: gate bits differ"
+        assert np.array_equal(got_dec, want_dec), f"{name} path {path}: decisions differ"
+        assert_metrics_match(m2, want_m, v2, want_v, rtol=1e-6, exact=True, what=f"{name} path {path}")
 
 
 def test_fp32_storage_matches_oracle_on_rounded_inputs():
@@ -136,8 +145,10 @@ def test_fp32_storage_matches_oracle_on_rounded_inputs():
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what="fp32")
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    got_dec, got_bits = gpu_fused(b)
-    assert np.array_equal(got_bits, want_bits) and np.array_equal(got_dec, want_dec)
+    for path in (1, 2):
+        got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
+        assert np.array_equal(got_bits, want_bits) and np.array_equal(got_dec, want_dec)
+        assert_metrics_match(m2, want_m, v2, want_v, rtol=1e-6, exact=True, what=f"fp32 path {path}")
 
 
 def test_start_ticks_has_previous_and_running_out_of_data():
@@ -147,8 +158,9 @@ def test_start_ticks_has_previous_and_running_out_of_data():
     st = rng.integers(0, p.n_ticks + 5, size=50).astype(np.int32)
     hp = (rng.random(50) < 0.8).astype(np.uint8)
     want, _ = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, has_previous=hp, start_tick=st)
-    got, _ = gpu_fused(b, has_previous=hp, start_tick=st)
-    assert np.array_equal(got, want)
+    for path in (1, 2):
+        got, _ = gpu_fused(b, has_previous=hp, start_tick=st, path=path)
+        assert np.array_equal(got, want), path
     assert (got[hp == 0, 2] == P.STATE_NO_CANARY).all()
     assert (got[:, 2] == P.STATE_IN_PROGRESS).any()     # some start too late to finish
 
