@@ -134,6 +134,9 @@ bool stream_eligible(const cg_params* p) {
     if (groups > 15 * 32) return false;
     const size_t slot = (size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p);
     if (slot >= (1u << 20)) return false;
+    // 32-bit time arithmetic in the kernel
+    if ((int64_t)p->tick0_ms + (int64_t)p->n_ticks * p->tick_step_ms >= (1ll << 30)) return false;
+    if ((int64_t)p->n_samples * p->period_ms >= (1ll << 30) || p->tick0_ms < -(1 << 30)) return false;
     const size_t fixed = (size_t)p->n_buckets * 8 + 3 * (((size_t)p->n_ticks + 31) / 32) * 4 + 2 * 32 * 8 + 256;
     return 3 * slot + fixed <= (size_t)kMaxSmem;
 }

@@ -55,6 +55,34 @@ CG_DEVINL TickGeom tick_geom(const cg_params& p, int32_t phase, int tick) {
     return g;
 }
 
+// Same as tick_geom with 32-bit integer arithmetic, for callers that have checked that every
+// time stamp involved fits in 31 bits (the streaming kernel's eligibility test).
+CG_DEVINL int floor_div32(int a, int b) {   // b > 0
+    int q = a / b;
+    return (a % b != 0 && a < 0) ? q - 1 : q;
+}
+CG_DEVINL TickGeom tick_geom32(const cg_params& p, int32_t phase, int tick) {
+    TickGeom g;
+    const int t  = p.tick0_ms + tick * p.tick_step_ms;
+    const int lo = t - p.window_ms;
+    int a = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+    int b = floor_div32(t - phase, p.period_ms);
+    if (a < 0) a = 0;
+    if (b > p.n_samples - 1) b = p.n_samples - 1;
+    g.i0 = a;
+    g.n  = b - a + 1;
+    if (g.n < 2) { g.n = g.n < 0 ? 0 : g.n; g.sampled = g.d_start = g.avg = g.thr = g.end_term = 0.0; return g; }
+    const int first_t = phase + a * p.period_ms;
+    const int last_t  = phase + b * p.period_ms;
+    g.d_start = (double)(first_t - lo) / 1000.0;
+    const double d_end = (double)(t - last_t) / 1000.0;
+    g.sampled = (double)(last_t - first_t) / 1000.0;
+    g.avg = g.sampled / (double)(g.n - 1);
+    g.thr = g.avg * 1.1;
+    g.end_term = (d_end < g.thr) ? d_end : g.avg / 2;
+    return g;
+}
+
 // Appendix A steps 4-6 for one series once `result` (step 2) is known.
 CG_DEVINL double extrapolate(double result, double first_v, const TickGeom& g) {
     double d_start = g.d_start;

@@ -71,31 +71,22 @@ template <> struct Tile6<float> {
 };
 
 // The three 4-sample windows a thread can need, at tile offsets 0, 1, 2 (Appendix A step 2:
-// last - first, then + the value before each counter reset, in time order).  Predicated adds
-// written in PTX so they stay one instruction each.
+// last - first, then + the value before each counter reset, in time order).  Counter resets are
+// rare, so the corrections are skipped when no lane of the warp saw one.  All 32 lanes call this.
+template <bool NEED_W2>
 __device__ __forceinline__ void windows3(const double (&x)[6], double& w0, double& w1, double& w2) {
-    asm("{\n\t"
-        ".reg .pred p1, p2, p3, p4, p5;\n\t"
-        "setp.lt.f64 p1, %4, %3;\n\t"
-        "setp.lt.f64 p2, %5, %4;\n\t"
-        "setp.lt.f64 p3, %6, %5;\n\t"
-        "setp.lt.f64 p4, %7, %6;\n\t"
-        "setp.lt.f64 p5, %8, %7;\n\t"
-        "sub.rn.f64 %0, %6, %3;\n\t"
-        "@p1 add.rn.f64 %0, %0, %3;\n\t"
-        "@p2 add.rn.f64 %0, %0, %4;\n\t"
-        "@p3 add.rn.f64 %0, %0, %5;\n\t"
-        "sub.rn.f64 %1, %7, %4;\n\t"
-        "@p2 add.rn.f64 %1, %1, %4;\n\t"
-        "@p3 add.rn.f64 %1, %1, %5;\n\t"
-        "@p4 add.rn.f64 %1, %1, %6;\n\t"
-        "sub.rn.f64 %2, %8, %5;\n\t"
-        "@p3 add.rn.f64 %2, %2, %5;\n\t"
-        "@p4 add.rn.f64 %2, %2, %6;\n\t"
-        "@p5 add.rn.f64 %2, %2, %7;\n\t"
-        "}"
-        : "=&d"(w0), "=&d"(w1), "=&d"(w2)
-        : "d"(x[0]), "d"(x[1]), "d"(x[2]), "d"(x[3]), "d"(x[4]), "d"(x[5]));
+    w0 = x[3] - x[0];
+    w1 = x[4] - x[1];
+    w2 = NEED_W2 ? x[5] - x[2] : 0.0;
+    const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3],
+               r5 = NEED_W2 && x[5] < x[4];
+    if (__any_sync(kFull, r1 | r2 | r3 | r4 | r5)) {
+        if (r1) w0 += x[0];
+        if (r2) { w0 += x[1]; w1 += x[1]; }
+        if (r3) { w0 += x[2]; w1 += x[2]; if (NEED_W2) w2 += x[2]; }
+        if (r4) { w1 += x[3]; if (NEED_W2) w2 += x[3]; }
+        if (r5) w2 += x[4];
+    }
 }
 
 // Per-thread state kept in REGISTERS across the rows of one (pair, version): only what every
@@ -248,14 +239,7 @@ static __device__ __noinline__ double slow_increase(double result, double first_
 }
 
 static __device__ __noinline__ TickGeom tick_geom_call(const cg_params& p, int32_t phase, int tick) {
-    return tick_geom(p, phase, tick);
-}
-
-template <int NQ>
-static __device__ __noinline__ void capture(Cold<NQ>* c, int q, int b, double cb, double cprev) {
-    c->bstar[q] = b;
-    c->cb[q] = cb;
-    c->cprev[q] = cprev;
+    return tick_geom32(p, phase, tick);
 }
 
 // ---- the rows of one (pair, version) -------------------------------------------------
@@ -277,20 +261,26 @@ __device__ __forceinline__ void consume_pv(const StreamArgs& a, unsigned char* r
     double x[6];                                                                                   \
     Tile6<T>::load((ROWPTR) + base, x);                                                            \
     double w0, w1, w2;                                                                             \
-    windows3(x, w0, w1, w2);                                                                       \
+    windows3<O2 == 2>(x, w0, w1, w2);                                                              \
     const double res[kG] = {w0, O1 == 0 ? w0 : w1, O2 == 1 ? w1 : w2};                             \
     const double fst[kG] = {x[0], x[O1], x[O2]};                                                   \
     double inc[kG];                                                                                \
+    bool slow[kG];                                                                                 \
     _Pragma("unroll") for (int s = 0; s < kG; ++s) {                                               \
-        if (fst[s] * h.gchk[s] >= res[s]) inc[s] = res[s] * h.f[s];                                \
-        else inc[s] = slow_increase(res[s], fst[s], cold[s].d_start, cold[s].end_term, sampled);   \
+        slow[s] = !(fst[s] * h.gchk[s] >= res[s]);                                                 \
+        inc[s] = res[s] * h.f[s];                                                                  \
+    }                                                                                              \
+    if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   /* rare: zero-point clamp may fire */  \
+        _Pragma("unroll") for (int s = 0; s < kG; ++s)                                             \
+            if (slow[s]) inc[s] = slow_increase(res[s], fst[s], cold[s].d_start, cold[s].end_term, sampled); \
     }
 
     for (int u = 0; u < n_use; ++u) {
         const uint32_t slot = it % (uint32_t)a.n_slots;
         mbar_wait(full_bar + slot, (it / (uint32_t)a.n_slots) & 1u);
         const T* rows = reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
-        if (active) {
+        if (!(p.reserved & 1)) {   // (reserved bit 0: debugging aid, skip the row math)
+            // every lane runs the row code (neutral factors for lanes without regular ticks)
             if (u < n_sc) {
                 // scalar counter rows: sum(increase(...)) per role, in series order
                 const int k0 = u * kRowsPerSlot, nr = min(kRowsPerSlot, K - k0);
@@ -315,25 +305,35 @@ __device__ __forceinline__ void consume_pv(const StreamArgs& a, unsigned char* r
                     cold[s].obs_inc = inc[s];
                     const double obs = inc[s] / range_s;
 #pragma unroll
-                    for (int q = 0; q < NQ; ++q) h.x0[s][q] = (p.q[q] * obs) * range_s;
+                    for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * range_s : NAN;
                 }
             } else {
                 const int b0 = (u - n_sc - 1) * kRowsPerSlot, nr = min(kRowsPerSlot, B - 1 - b0);
 #pragma unroll 1
                 for (int k = 0; k < nr; ++k) {
                     CG_ROW_INCREASES(rows + k * pitch)
+                    double c[kG];
+                    bool any_hit = false;
 #pragma unroll
                     for (int s = 0; s < kG; ++s) {
-                        double c = inc[s];
-                        if (c < h.prev[s]) c = h.prev[s];            // monotonic fix (Appendix A step 3)
+                        c[s] = inc[s] < h.prev[s] ? h.prev[s] : inc[s];   // monotonic fix (Appendix A step 3)
 #pragma unroll
-                        for (int q = 0; q < NQ; ++q)
-                            if (c >= h.x0[s][q]) {                   // first bucket reaching the rank
-                                capture<NQ>(cold + s, q, b0 + k, c, h.prev[s]);
-                                h.x0[s][q] = NAN;                    // never true again
-                            }
-                        h.prev[s] = c;
+                        for (int q = 0; q < NQ; ++q) any_hit |= c[s] >= h.x0[s][q];
                     }
+                    if (__any_sync(kFull, any_hit)) {       // some lane's first bucket reaching the rank
+#pragma unroll
+                        for (int s = 0; s < kG; ++s)
+#pragma unroll
+                            for (int q = 0; q < NQ; ++q)
+                                if (c[s] >= h.x0[s][q]) {
+                                    cold[s].bstar[q] = b0 + k;
+                                    cold[s].cb[q] = c[s];
+                                    cold[s].cprev[q] = h.prev[s];
+                                    h.x0[s][q] = NAN;       // never true again
+                                }
+                    }
+#pragma unroll
+                    for (int s = 0; s < kG; ++s) h.prev[s] = c[s];
                 }
             }
         }
@@ -344,91 +344,19 @@ __device__ __forceinline__ void consume_pv(const StreamArgs& a, unsigned char* r
 #undef CG_ROW_INCREASES
 }
 
-template <typename T, int NQ, int CW>
-__global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 3 : 1)
-stream_kernel(const __grid_constant__ StreamArgs a) {
-    extern __shared__ __align__(128) unsigned char smem[];
+// Everything one consumer thread does for one (pair, version): tick geometry, the row stream,
+// the per-tick finish and the exact fallback.  Kept out of line so that its registers are not
+// live across the two versions of a pair.  -> m[s][*], v[s] for the thread's kG ticks.
+template <typename T, int NQ>
+static __device__ __forceinline__ void run_version(const StreamArgs& a, unsigned char* ring, uint64_t* full_bar,
+                                                uint64_t* empty_bar, const double* s_le, uint32_t& it,
+                                                int64_t pv, int grp, bool has_ticks, int lane,
+                                                double (*m)[CG_MAX_Q + CG_M_EXTRA], uint8_t* v) {
     const cg_params& p = a.p;
-    unsigned char* ring = smem;
-    double*   s_le   = reinterpret_cast<double*>(smem + a.off_le);
-    uint32_t* s_bits = reinterpret_cast<uint32_t*>(smem + a.off_bits);
-    uint64_t* full_bar  = reinterpret_cast<uint64_t*>(smem + a.off_bars);
-    uint64_t* empty_bar = full_bar + a.n_slots;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n_cons = a.consumer_warps * 32;
-    const int K = p.n_scalar, B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
-    const int n_words = (p.n_ticks + 31) >> 5;
-    if (tid == 0) {
-        for (int s = 0; s < a.n_slots; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, a.consumer_warps); }
-        mbar_init_fence();
-    }
-    for (int b = tid; b < B; b += blockDim.x) s_le[b] = a.le[b];
-    for (int w = tid; w < 3 * n_words; w += blockDim.x) s_bits[w] = 0u;
-    __syncthreads();
-
-    const size_t row_bytes = (size_t)p.row_pitch * sizeof(T);
-
-    if (warp == a.consumer_warps) {
-        // ===== producer: one elected lane drives the TMA bulk-copy engine =====
-        if (lane == 0) {
-            uint32_t it = 0;
-            auto push = [&](const char* src, uint32_t bytes) {
-                const uint32_t slot = it % (uint32_t)a.n_slots;
-                mbar_wait(empty_bar + slot, ((it / (uint32_t)a.n_slots) & 1u) ^ 1u);
-                mbar_arrive_expect_tx(full_bar + slot, bytes);
-                bulk_g2s(ring + (size_t)slot * a.slot_bytes, src, bytes, full_bar + slot);
-                ++it;
-            };
-            for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
-                if (a.has_previous && !a.has_previous[pair]) continue;
-                for (int ver = 0; ver < 2; ++ver) {
-                    const int64_t pv = pair * 2 + ver;
-                    const char* gs = reinterpret_cast<const char*>(a.scalars) + (size_t)pv * K * row_bytes;
-                    const char* gb = reinterpret_cast<const char*>(a.buckets) + (size_t)pv * B * row_bytes;
-                    for (int k0 = 0; k0 < K; k0 += kRowsPerSlot)
-                        push(gs + (size_t)k0 * row_bytes, (uint32_t)(min(kRowsPerSlot, K - k0) * row_bytes));
-                    if (B > 0) {
-                        push(gb + (size_t)(B - 1) * row_bytes, (uint32_t)row_bytes);
-                        for (int b0 = 0; b0 < B - 1; b0 += kRowsPerSlot)
-                            push(gb + (size_t)b0 * row_bytes, (uint32_t)(min(kRowsPerSlot, B - 1 - b0) * row_bytes));
-                    }
-                }
-            }
-        }
-        return;
-    }
-
-    // ===== consumers =====
-    const int grp = tid;                       // thread <-> period of the tick grid
-    const bool has_ticks = grp < a.n_groups;
+    const int B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
     const double range_s = (double)p.window_ms / 1000.0;
-    uint32_t it = 0;
-    int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
-
-    for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
-        const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
-        const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
-        if (!hp) {
-            if (tid == 0) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
-            if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = 0u;
-            continue;
-        }
-        uint32_t* bits = s_bits + bit_buf * n_words;
-        {   // Clear the buffer the NEXT pair will use.  It was last read right after the barrier
-            // two pairs ago, and every thread has passed the barrier one pair ago since, so no
-            // reader is left; the next pair's atomicOr comes after this pair's barrier.
-            uint32_t* nxt = s_bits + ((bit_buf + 1) % 3) * n_words;
-            for (int w = tid; w < n_words; w += n_cons) nxt[w] = 0u;
-        }
-        double nm[kG][3];          // the new version's gate inputs, kept for the old version's pass
-        uint8_t nv[kG];
-#pragma unroll
-        for (int s = 0; s < kG; ++s) { nm[s][0] = nm[s][1] = nm[s][2] = NAN; nv[s] = 0; }
-
-        for (int ver = 0; ver < 2; ++ver) {
-            const int64_t pv = pair * 2 + ver;
-            const int32_t phase = a.phase[pv];
+    const int32_t phase = a.phase[pv];
+    {
             Hot<NQ> h;
             Cold<NQ> cold[kG];
             int base = 0;
@@ -461,44 +389,53 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     }
                 }
             }
-            // pattern of the interior groups, from the phase alone (uniform across the CTA)
+            // A thread is self-regular if every tick it owns has a 4-sample window starting at an
+            // even sample; the window pattern (O1, O2) of such threads depends only on the phase.
+            bool self_ok = has_ticks && cold[0].tick < p.n_ticks && (cold[0].flags & kRegular) &&
+                           (base & 1) == 0 && base >= 0;
+            bool full_group = true;
+#pragma unroll
+            for (int s = 1; s < kG; ++s) {
+                if (has_ticks && cold[s].tick < p.n_ticks) { if (!(cold[s].flags & kRegular)) self_ok = false; }
+                else full_group = false;
+            }
             int O1 = 0, O2 = 1;
-            {
-                const int gi = a.n_groups > 2 ? 1 : 0;
-                const TickGeom g0 = tick_geom_call(p, phase, gi * kG), g1 = tick_geom_call(p, phase, gi * kG + 1),
-                               g2 = tick_geom_call(p, phase, gi * kG + 2);
-                O1 = g1.i0 - g0.i0; O2 = g2.i0 - g0.i0;
+            {   // the warp adopts the pattern of its first self-regular lane with a full group
+                const unsigned cand = __ballot_sync(kFull, self_ok && full_group);
+                const int src = cand ? __ffs(cand) - 1 : 0;
+                O1 = __shfl_sync(kFull, off[1], src);
+                O2 = __shfl_sync(kFull, off[2], src);
+                if (!cand) { O1 = 0; O2 = 1; }
             }
             const bool pat_ok = (O1 == 0 && O2 == 1) || (O1 == 1 && O2 == 1) || (O1 == 1 && O2 == 2);
-            // a thread runs the fast path only if all of its ticks are regular and match the pattern
-            bool active = has_ticks && pat_ok && (base & 1) == 0 && base >= 0;
+            bool active = self_ok && pat_ok;
 #pragma unroll
-            for (int s = 0; s < kG; ++s) {
-                const bool exists = has_ticks && cold[s].tick < p.n_ticks;
-                const int want = s == 0 ? 0 : (s == 1 ? O1 : O2);
-                if (exists && !((cold[s].flags & kRegular) && off[s] == want)) active = false;
-            }
-            if (has_ticks && cold[0].tick >= p.n_ticks) active = false;
+            for (int s = 1; s < kG; ++s)
+                if (has_ticks && cold[s].tick < p.n_ticks && off[s] != (s == 1 ? O1 : O2)) active = false;
             if (!active) {
+                // neutral row code: loads stay inside the row, nothing is captured; the ticks
+                // (if any) are evaluated exactly by the whole warp afterwards
+                base = 0;
 #pragma unroll
-                for (int s = 0; s < kG; ++s)
+                for (int s = 0; s < kG; ++s) {
+                    h.f[s] = 0.0; h.gchk[s] = INFINITY;
                     if (has_ticks && cold[s].tick < p.n_ticks) cold[s].flags |= kFallback;
+                }
             } else {
-                // slots of a partial last group reuse tick 0's factors so the row code stays
-                // branch-free; their results are never read
+                // slots of a partial last group reuse tick 0's factors; their results are never read
 #pragma unroll
                 for (int s = 1; s < kG; ++s)
                     if (!(cold[s].tick < p.n_ticks)) { h.f[s] = h.f[0]; h.gchk[s] = INFINITY; }
             }
+            if (!pat_ok) { O1 = 0; O2 = 1; }
 
             // ---- stream the rows
             if (O1 == 0) consume_pv<T, NQ, 0, 1>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
             else if (O2 == 1) consume_pv<T, NQ, 1, 1>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
             else consume_pv<T, NQ, 1, 2>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
 
+            if (p.reserved & 2) return;   // (reserved bit 1: debugging aid, skip the per-tick finish)
             // ---- finish each tick: histogram_quantile, ratios, validity
-            double m[kG][CG_MAX_Q + CG_M_EXTRA];
-            uint8_t v[kG];
 #pragma unroll 1
             for (int s = 0; s < kG; ++s) {
                 Cold<NQ>& t = cold[s];
@@ -567,10 +504,105 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     }
                 }
             }
+    }
+}
+
+template <typename T, int NQ, int CW>
+__global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 3 : 1)
+stream_kernel(const __grid_constant__ StreamArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const cg_params& p = a.p;
+    unsigned char* ring = smem;
+    double*   s_le   = reinterpret_cast<double*>(smem + a.off_le);
+    uint32_t* s_bits = reinterpret_cast<uint32_t*>(smem + a.off_bits);
+    uint64_t* full_bar  = reinterpret_cast<uint64_t*>(smem + a.off_bars);
+    uint64_t* empty_bar = full_bar + a.n_slots;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_cons = a.consumer_warps * 32;
+    const int K = p.n_scalar, B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
+    const int n_words = (p.n_ticks + 31) >> 5;
+    if (tid == 0) {
+        for (int s = 0; s < a.n_slots; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, a.consumer_warps); }
+        mbar_init_fence();
+    }
+    for (int b = tid; b < B; b += blockDim.x) s_le[b] = a.le[b];
+    for (int w = tid; w < 3 * n_words; w += blockDim.x) s_bits[w] = 0u;
+    __syncthreads();
+
+    const size_t row_bytes = (size_t)p.row_pitch * sizeof(T);
+
+    if (warp == a.consumer_warps) {
+        // ===== producer: one elected lane drives the TMA bulk-copy engine =====
+        if (lane == 0) {
+            uint32_t it = 0;
+            auto push = [&](const char* src, uint32_t bytes) {
+                const uint32_t slot = it % (uint32_t)a.n_slots;
+                mbar_wait_backoff(empty_bar + slot, ((it / (uint32_t)a.n_slots) & 1u) ^ 1u);
+                mbar_arrive_expect_tx(full_bar + slot, bytes);
+                bulk_g2s(ring + (size_t)slot * a.slot_bytes, src, bytes, full_bar + slot);
+                ++it;
+            };
+            for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
+                if (a.has_previous && !a.has_previous[pair]) continue;
+                for (int ver = 0; ver < 2; ++ver) {
+                    const int64_t pv = pair * 2 + ver;
+                    const char* gs = reinterpret_cast<const char*>(a.scalars) + (size_t)pv * K * row_bytes;
+                    const char* gb = reinterpret_cast<const char*>(a.buckets) + (size_t)pv * B * row_bytes;
+                    for (int k0 = 0; k0 < K; k0 += kRowsPerSlot)
+                        push(gs + (size_t)k0 * row_bytes, (uint32_t)(min(kRowsPerSlot, K - k0) * row_bytes));
+                    if (B > 0) {
+                        push(gb + (size_t)(B - 1) * row_bytes, (uint32_t)row_bytes);
+                        for (int b0 = 0; b0 < B - 1; b0 += kRowsPerSlot)
+                            push(gb + (size_t)b0 * row_bytes, (uint32_t)(min(kRowsPerSlot, B - 1 - b0) * row_bytes));
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers =====
+    const int grp = tid;                       // thread <-> period of the tick grid
+    const bool has_ticks = grp < a.n_groups;
+    const double range_s = (double)p.window_ms / 1000.0;
+    uint32_t it = 0;
+    int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
+
+    for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
+        const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
+        const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
+        if (!hp) {
+            if (tid == 0) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
+            if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = 0u;
+            continue;
+        }
+        uint32_t* bits = s_bits + bit_buf * n_words;
+        {   // Clear the buffer the NEXT pair will use.  It was last read right after the barrier
+            // two pairs ago, and every thread has passed the barrier one pair ago since, so no
+            // reader is left; the next pair's atomicOr comes after this pair's barrier.
+            uint32_t* nxt = s_bits + ((bit_buf + 1) % 3) * n_words;
+            for (int w = tid; w < n_words; w += n_cons) nxt[w] = 0u;
+        }
+        double nm[kG][3];          // the new version's gate inputs, kept for the old version's pass
+        uint8_t nv[kG];
+#pragma unroll
+        for (int s = 0; s < kG; ++s) { nm[s][0] = nm[s][1] = nm[s][2] = NAN; nv[s] = 0; }
+
+        for (int ver = 0; ver < 2; ++ver) {
+            const int64_t pv = pair * 2 + ver;
+            double m[kG][CG_MAX_Q + CG_M_EXTRA];
+            uint8_t v[kG];
+#pragma unroll
+            for (int s = 0; s < kG; ++s) v[s] = 0;
+            run_version<T, NQ>(a, ring, full_bar, empty_bar, s_le, it, pv, grp, has_ticks, lane, m, v);
+            int tick_of[kG];
+#pragma unroll
+            for (int s = 0; s < kG; ++s) tick_of[s] = grp * kG + s;
             // ---- outputs of this version; gate once both are known
 #pragma unroll
             for (int s = 0; s < kG; ++s) {
-                const int tk = cold[s].tick;
+                const int tk = tick_of[s];
                 if (!(has_ticks && tk < p.n_ticks)) continue;
                 if (a.metrics) {
                     double* o = a.metrics + ((size_t)pv * p.n_ticks + tk) * W;

@@ -13,6 +13,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 path = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 p = P.make_params()
+p.reserved = int(os.environ.get('CG_DEBUG', '0'))
 le = torch.from_numpy(synth.default_le(p.n_buckets)).cuda()
 sc, bk, ph = engine.synth_fill(n, p, le, seed=0xC0FFEE + 3)
 torch.cuda.synchronize()
