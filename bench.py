@@ -176,7 +176,7 @@ def main():
     import numpy as np
     import torch
     import canary_b200  # noqa: F401
-    from canary_b200 import _lib, engine, params as P, synth
+    from canary_b200 import _lib, engine, params as P, sharding, synth
     from oracle import c_oracle as co      # checker + cpu_baseline leg only
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -198,13 +198,14 @@ def main():
     bytes_per_pair = p.bytes_per_pair()
 
     # decisions live in one gather buffer; each rank's kernel writes its own slice in place
-    gathered = torch.empty((world * n, 6), dtype=torch.int32, device=dev)
-    mine = gathered[rank * n:(rank + 1) * n]
+    n_total = world * n
+    gathered = sharding.alloc_gather_buffer(n_total, world, dev)
+    mine = sharding.my_slice(gathered, n_total, rank, world)
 
     def step():
         engine.eval_fused(scalars, buckets, le, phase, p, out=mine)
         if dist is not None:
-            dist.all_gather_into_tensor(gathered, mine)
+            sharding.gather_decisions(gathered, n_total)
 
     # ---- parity spot check against the oracle before timing anything
     step()
@@ -230,7 +231,7 @@ def main():
             engine.eval_fused(scalars, buckets, le, phase, p, out=mine)
             ev[2 + 2 * i].record(stream)
             if dist is not None:
-                dist.all_gather_into_tensor(gathered, mine)
+                sharding.gather_decisions(gathered, n_total)
         ev[-1].record(stream)
         torch.cuda.synchronize()
     launches = _lib.launch_count() - launches0
