@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <atomic>
 
 #include "../../include/canary_gate.h"
@@ -125,6 +126,16 @@ struct StreamPlan {
     int grid, block, cw_template;
 };
 
+// doubles per thread of the streaming kernel's shared-memory record (cg::Rec<NQ>::kDoubles)
+int rec_doubles(int n_q) {
+    switch (n_q <= 1 ? 1 : n_q) {
+        case 1: return cg::Rec<1>::kDoubles;
+        case 2: return cg::Rec<2>::kDoubles;
+        case 3: return cg::Rec<3>::kDoubles;
+        default: return cg::Rec<4>::kDoubles;
+    }
+}
+
 bool stream_eligible(const cg_params* p) {
     if ((int64_t)p->window_ms != 4 * (int64_t)p->period_ms) return false;
     if (3 * (int64_t)p->tick_step_ms != 2 * (int64_t)p->period_ms) return false;
@@ -137,7 +148,8 @@ bool stream_eligible(const cg_params* p) {
     // 32-bit time arithmetic in the kernel
     if ((int64_t)p->tick0_ms + (int64_t)p->n_ticks * p->tick_step_ms >= (1ll << 30)) return false;
     if ((int64_t)p->n_samples * p->period_ms >= (1ll << 30) || p->tick0_ms < -(1 << 30)) return false;
-    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * (((size_t)p->n_ticks + 31) / 32) * 4 + 2 * 32 * 8 + 256;
+    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * (((size_t)p->n_ticks + 31) / 32) * 4 + 2 * 32 * 8 + 256 +
+                         (size_t)((groups + 31) / 32) * 32 * rec_doubles(p->n_q) * 8;
     return 3 * slot + fixed <= (size_t)kMaxSmem;
 }
 
@@ -151,7 +163,18 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     plan->cw_template = a.consumer_warps <= 4 ? 4 : 15;
     a.slot_bytes = (uint32_t)((size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p));
     const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
-    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * n_words * 4 + 2 * 32 * 8 + 256;
+    a.range_s = (double)p->window_ms / 1000.0;
+    a.rc_range = 1.0 / a.range_s;
+    a.sampled = (double)(3 * (int64_t)p->period_ms) / 1000.0;
+    a.rc_sampled = 1.0 / a.sampled;
+    {
+        const double avg = a.sampled / 3.0;     // sampled / (n - 1), n = 4
+        a.thr = avg * 1.1;
+        a.half_avg = avg / 2;
+    }
+    a.rec_doubles = rec_doubles(p->n_q);
+    const size_t rec = (size_t)a.consumer_warps * 32 * a.rec_doubles * 8;
+    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * n_words * 4 + 2 * 32 * 8 + 256 + rec;
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
@@ -167,12 +190,14 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     }
     if (slots < 3) return fail(CG_EINVAL, "streaming kernel: ring does not fit shared memory");
     if (slots > 32) slots = 32;
+    if (const char* e = getenv("CG_STREAM_SLOTS")) { int v = atoi(e); if (v >= 3 && v < slots) slots = v; }   // tuning aid
     a.n_slots = slots;
     size_t off = (size_t)slots * a.slot_bytes;
     a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
     a.off_bits = (uint32_t)off; off += 3 * n_words * 4;
     off = (off + 7) & ~(size_t)7;
     a.off_bars = (uint32_t)off; off += (size_t)2 * slots * 8;
+    a.off_rec = (uint32_t)off; off += rec;
     a.smem_bytes = (uint32_t)off;
     plan->block = threads;
     int64_t g = (int64_t)sms * per_sm;

@@ -55,6 +55,21 @@ CG_DEVINL TickGeom tick_geom(const cg_params& p, int32_t phase, int tick) {
     return g;
 }
 
+// a / c for a constant c with rc = 1/c correctly rounded: the Markstein sequence
+// (q = a*rc; r = fma(-q, c, a); q + r*rc) gives the correctly rounded quotient, i.e. exactly what
+// IEEE division gives, in three operations instead of the ~120-cycle division routine.  Checked
+// against true division on 2e8 random doubles over 80 binades and every integer in [-3e5, 4e6]
+// for each constant used here (tests/test_div_const.py keeps a smaller version of that check).
+// Magnitudes near the overflow / underflow ends take the true division.
+CG_DEVINL double div_const(double a, double c, double rc) {
+    const double q = a * rc;
+    const double r = fma(-q, c, a);
+    const double q2 = fma(r, rc, q);
+    const double aa = fabs(a);
+    if (!(aa < 1e300 && (aa > 1e-290 || a == 0.0))) return a / c;
+    return q2;
+}
+
 // Same as tick_geom with 32-bit integer arithmetic, for callers that have checked that every
 // time stamp involved fits in 31 bits (the streaming kernel's eligibility test).
 CG_DEVINL int floor_div32(int a, int b) {   // b > 0

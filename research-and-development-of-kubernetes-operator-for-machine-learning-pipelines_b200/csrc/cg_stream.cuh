@@ -50,7 +50,12 @@ struct StreamArgs {
     int32_t  consumer_warps;
     int32_t  n_slots;
     uint32_t slot_bytes;           // kRowsPerSlot * row_pitch * sizeof(elem)
-    uint32_t off_le, off_bits, off_bars, smem_bytes;
+    uint32_t off_le, off_bits, off_bars, off_rec, smem_bytes;
+    // host-computed constants of a regular 4-sample window (all exact IEEE operations)
+    double   range_s, rc_range;        // window_ms/1000 and its reciprocal
+    double   sampled, rc_sampled;      // 3*period_ms/1000 and its reciprocal
+    double   thr, half_avg;            // (sampled/3)*1.1 and (sampled/3)/2
+    int32_t  rec_doubles;              // doubles per thread in the shared-memory record
 };
 
 // ---- 6-sample register tile ---------------------------------------------------------
@@ -70,27 +75,11 @@ template <> struct Tile6<float> {
     }
 };
 
-// The three 4-sample windows a thread can need, at tile offsets 0, 1, 2 (Appendix A step 2:
-// last - first, then + the value before each counter reset, in time order).  Counter resets are
-// rare, so the corrections are skipped when no lane of the warp saw one.  All 32 lanes call this.
-template <bool NEED_W2>
-__device__ __forceinline__ void windows3(const double (&x)[6], double& w0, double& w1, double& w2) {
-    w0 = x[3] - x[0];
-    w1 = x[4] - x[1];
-    w2 = NEED_W2 ? x[5] - x[2] : 0.0;
-    const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3],
-               r5 = NEED_W2 && x[5] < x[4];
-    if (__any_sync(kFull, r1 | r2 | r3 | r4 | r5)) {
-        if (r1) w0 += x[0];
-        if (r2) { w0 += x[1]; w1 += x[1]; }
-        if (r3) { w0 += x[2]; w1 += x[2]; if (NEED_W2) w2 += x[2]; }
-        if (r4) { w1 += x[3]; if (NEED_W2) w2 += x[3]; }
-        if (r5) w2 += x[4];
-    }
-}
-
-// Per-thread state kept in REGISTERS across the rows of one (pair, version): only what every
-// row touches.
+// ---- per-thread state ------------------------------------------------------------------
+// Registers hold only what every row touches.  Everything touched rarely (captured search
+// results, observations, the derived ratios, the other version's gate inputs) lives in SHARED
+// memory as structure-of-arrays records [field][thread]: with most of the 228 KB of an SM carved
+// out for the row ring, L1 is too small to back local-memory arrays, so none are used.
 template <int NQ>
 struct Hot {
     double f[kG];        // ext/sampled with the unclamped d_start (Appendix A step 5-6)
@@ -99,20 +88,18 @@ struct Hot {
     double x0[kG][NQ];   // search threshold in increase space (rank * range_s); NaN once found
 };
 
-// Per-thread state touched rarely: lives in local memory (indexed dynamically on purpose).
 template <int NQ>
-struct Cold {
-    double d_start, end_term;        // for the exact clamp path
-    double obs_inc;                  // increase of the +Inf bucket
-    double cb[NQ], cprev[NQ];        // fixed counts at / before the bucket that reaches the rank
-    int    bstar[NQ];
-    double sums[5];                  // Q3, Q2, Q4, Q5, Q6 in role-bit order
-    unsigned have;
-    unsigned flags;                  // kRegular | kFallback
-    int    tick;
+struct Rec {                       // field indices of the shared-memory record (in doubles)
+    static constexpr int kObs   = 0;                   // [kG]      increase of the +Inf bucket
+    static constexpr int kCb    = kObs + kG;           // [kG][NQ]  fixed count at the bucket reaching the rank
+    static constexpr int kCprev = kCb + kG * NQ;       // [kG][NQ]  fixed count just before it
+    static constexpr int kEr    = kCprev + kG * NQ;    // [kG]      error_rate of this version
+    static constexpr int kAvg   = kEr + kG;            // [kG]      latency_avg of this version
+    static constexpr int kQv    = kAvg + kG;           // [kG]      gate quantile of this version
+    static constexpr int kStash = kQv + kG;            // [kG][3]   the NEW version's gate inputs
+    static constexpr int kInts  = kStash + kG * 3;     // then (kG*NQ + 2) ints: bstar, valid, stash valid
+    static constexpr int kDoubles = kInts + (kG * NQ + 2 + 1) / 2;
 };
-
-constexpr unsigned kRegular = 1u, kFallback = 2u;
 
 // ---- warp-cooperative exact evaluation of one (pair, version, tick) from global memory
 template <typename T>
@@ -225,292 +212,73 @@ __device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int
 }
 
 // Rare path of a fast row: the zero-point clamp may fire -> exact Appendix A step 4-6 for a
-// regular 4-sample window (sampled interval = 3 scrape periods).
-static __device__ __noinline__ double slow_increase(double result, double first_v, double d_start,
-                                                    double end_term, double sampled) {
+// regular 4-sample window; its two tick-dependent terms are recomputed from the time stamps.
+static __device__ __noinline__ double slow_increase(const StreamArgs& a, int32_t phase, int tick, double result,
+                                                    double first_v) {
+    const cg_params& p = a.p;
+    const int t = p.tick0_ms + tick * p.tick_step_ms, lo = t - p.window_ms;
+    int i0 = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+    int i1 = floor_div32(t - phase, p.period_ms);
+    if (i0 < 0) i0 = 0;
+    if (i1 > p.n_samples - 1) i1 = p.n_samples - 1;
     TickGeom g;
-    g.i0 = 0; g.n = 4;
-    g.sampled = sampled;
-    g.d_start = d_start;
-    g.avg = sampled / 3.0;
-    g.thr = g.avg * 1.1;
-    g.end_term = end_term;
+    g.i0 = i0; g.n = 4;
+    g.sampled = a.sampled;
+    g.d_start = div_const((double)(phase + i0 * p.period_ms - lo), 1000.0, 1e-3);
+    const double d_end = div_const((double)(t - (phase + i1 * p.period_ms)), 1000.0, 1e-3);
+    g.avg = a.half_avg + a.half_avg;
+    g.thr = a.thr;
+    g.end_term = (d_end < a.thr) ? d_end : a.half_avg;
     return extrapolate(result, first_v, g);
 }
 
-static __device__ __noinline__ TickGeom tick_geom_call(const cg_params& p, int32_t phase, int tick) {
-    return tick_geom32(p, phase, tick);
-}
-
-// ---- the rows of one (pair, version) -------------------------------------------------
-// O1 / O2: tile offsets of the windows of tick 1 and tick 2 (tick 0 is at offset 0).  The three
-// patterns that occur are (0,1), (1,1), (1,2); the choice depends only on the series phase.
+// Window deltas and fast increases of one row for the thread's kG ticks.  O1 / O2: tile offsets of
+// the windows of tick 1 and tick 2 (tick 0 is at offset 0); the patterns that occur are (0,1),
+// (1,1), (1,2) and depend only on the series phase.  All 32 lanes call this.
 template <typename T, int NQ, int O1, int O2>
-__device__ __forceinline__ void consume_pv(const StreamArgs& a, unsigned char* ring, uint64_t* full_bar,
-                                           uint64_t* empty_bar, uint32_t& it, int base, Hot<NQ>& h,
-                                           Cold<NQ>* cold, bool active, int lane) {
-    const cg_params& p = a.p;
-    const int K = p.n_scalar, B = p.n_buckets;
-    const size_t pitch = p.row_pitch;
-    const double range_s = (double)p.window_ms / 1000.0;
-    const double sampled = (double)(3 * p.period_ms) / 1000.0;
-    const int n_sc = (K + kRowsPerSlot - 1) / kRowsPerSlot;
-    const int n_use = n_sc + (B > 0 ? 1 + (B - 1 + kRowsPerSlot - 1) / kRowsPerSlot : 0);
-
-#define CG_ROW_INCREASES(ROWPTR)                                                                   \
-    double x[6];                                                                                   \
-    Tile6<T>::load((ROWPTR) + base, x);                                                            \
-    double w0, w1, w2;                                                                             \
-    windows3<O2 == 2>(x, w0, w1, w2);                                                              \
-    const double res[kG] = {w0, O1 == 0 ? w0 : w1, O2 == 1 ? w1 : w2};                             \
-    const double fst[kG] = {x[0], x[O1], x[O2]};                                                   \
-    double inc[kG];                                                                                \
-    bool slow[kG];                                                                                 \
-    _Pragma("unroll") for (int s = 0; s < kG; ++s) {                                               \
-        slow[s] = !(fst[s] * h.gchk[s] >= res[s]);                                                 \
-        inc[s] = res[s] * h.f[s];                                                                  \
-    }                                                                                              \
-    if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   /* rare: zero-point clamp may fire */  \
-        _Pragma("unroll") for (int s = 0; s < kG; ++s)                                             \
-            if (slow[s]) inc[s] = slow_increase(res[s], fst[s], cold[s].d_start, cold[s].end_term, sampled); \
+__device__ __forceinline__ void row_increases(const T* __restrict__ row, const Hot<NQ>& h, const StreamArgs& a,
+                                              const int32_t phase, const int tick0, double (&inc)[kG]) {
+    double x[6];
+    Tile6<T>::load(row, x);
+    double w0 = x[3] - x[0], w1 = x[4] - x[1], w2 = (O2 == 2) ? x[5] - x[2] : 0.0;
+    const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3],
+               r5 = (O2 == 2) && x[5] < x[4];
+    if (__any_sync(kFull, r1 | r2 | r3 | r4 | r5)) {   // counter resets are rare (Appendix A step 2)
+        if (r1) w0 += x[0];
+        if (r2) { w0 += x[1]; w1 += x[1]; }
+        if (r3) { w0 += x[2]; w1 += x[2]; if (O2 == 2) w2 += x[2]; }
+        if (r4) { w1 += x[3]; if (O2 == 2) w2 += x[3]; }
+        if (r5) w2 += x[4];
     }
-
-    for (int u = 0; u < n_use; ++u) {
-        const uint32_t slot = it % (uint32_t)a.n_slots;
-        mbar_wait(full_bar + slot, (it / (uint32_t)a.n_slots) & 1u);
-        const T* rows = reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
-        if (!(p.reserved & 1)) {   // (reserved bit 0: debugging aid, skip the row math)
-            // every lane runs the row code (neutral factors for lanes without regular ticks)
-            if (u < n_sc) {
-                // scalar counter rows: sum(increase(...)) per role, in series order
-                const int k0 = u * kRowsPerSlot, nr = min(kRowsPerSlot, K - k0);
-#pragma unroll 1
-                for (int k = 0; k < nr; ++k) {
-                    CG_ROW_INCREASES(rows + k * pitch)
-                    const unsigned role = p.scalar_role[k0 + k];
+    const double res[kG] = {w0, O1 == 0 ? w0 : w1, O2 == 1 ? w1 : w2};
+    const double fst[kG] = {x[0], x[O1], x[O2]};
+    bool slow[kG];
 #pragma unroll
-                    for (int s = 0; s < kG; ++s)
-#pragma unroll
-                        for (int q = 0; q < 5; ++q)
-                            if (role & (1u << q)) {
-                                cold[s].sums[q] = (cold[s].have & (1u << q)) ? cold[s].sums[q] + inc[s] : inc[s];
-                                cold[s].have |= 1u << q;
-                            }
-                }
-            } else if (u == n_sc) {
-                // the +Inf bucket first: observations -> rank -> search threshold
-                CG_ROW_INCREASES(rows)
-#pragma unroll
-                for (int s = 0; s < kG; ++s) {
-                    cold[s].obs_inc = inc[s];
-                    const double obs = inc[s] / range_s;
-#pragma unroll
-                    for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * range_s : NAN;
-                }
-            } else {
-                const int b0 = (u - n_sc - 1) * kRowsPerSlot, nr = min(kRowsPerSlot, B - 1 - b0);
-#pragma unroll 1
-                for (int k = 0; k < nr; ++k) {
-                    CG_ROW_INCREASES(rows + k * pitch)
-                    double c[kG];
-                    bool any_hit = false;
-#pragma unroll
-                    for (int s = 0; s < kG; ++s) {
-                        c[s] = inc[s] < h.prev[s] ? h.prev[s] : inc[s];   // monotonic fix (Appendix A step 3)
-#pragma unroll
-                        for (int q = 0; q < NQ; ++q) any_hit |= c[s] >= h.x0[s][q];
-                    }
-                    if (__any_sync(kFull, any_hit)) {       // some lane's first bucket reaching the rank
-#pragma unroll
-                        for (int s = 0; s < kG; ++s)
-#pragma unroll
-                            for (int q = 0; q < NQ; ++q)
-                                if (c[s] >= h.x0[s][q]) {
-                                    cold[s].bstar[q] = b0 + k;
-                                    cold[s].cb[q] = c[s];
-                                    cold[s].cprev[q] = h.prev[s];
-                                    h.x0[s][q] = NAN;       // never true again
-                                }
-                    }
-#pragma unroll
-                    for (int s = 0; s < kG; ++s) h.prev[s] = c[s];
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty_bar + slot);
-        ++it;
+    for (int s = 0; s < kG; ++s) {
+        slow[s] = !(fst[s] * h.gchk[s] >= res[s]);
+        inc[s] = res[s] * h.f[s];
     }
-#undef CG_ROW_INCREASES
+    if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   // rare: the zero-point clamp may fire
+#pragma unroll
+        for (int s = 0; s < kG; ++s)
+            if (slow[s]) inc[s] = slow_increase(a, phase, tick0 + s, res[s], fst[s]);
+    }
 }
 
-// Everything one consumer thread does for one (pair, version): tick geometry, the row stream,
-// the per-tick finish and the exact fallback.  Kept out of line so that its registers are not
-// live across the two versions of a pair.  -> m[s][*], v[s] for the thread's kG ticks.
 template <typename T, int NQ>
-static __device__ __forceinline__ void run_version(const StreamArgs& a, unsigned char* ring, uint64_t* full_bar,
-                                                uint64_t* empty_bar, const double* s_le, uint32_t& it,
-                                                int64_t pv, int grp, bool has_ticks, int lane,
-                                                double (*m)[CG_MAX_Q + CG_M_EXTRA], uint8_t* v) {
-    const cg_params& p = a.p;
-    const int B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
-    const double range_s = (double)p.window_ms / 1000.0;
-    const int32_t phase = a.phase[pv];
-    {
-            Hot<NQ> h;
-            Cold<NQ> cold[kG];
-            int base = 0;
-            // ---- per-thread tick geometry and the CTA-uniform window pattern
-            int off[kG];
-#pragma unroll
-            for (int s = 0; s < kG; ++s) {
-                Cold<NQ>& c = cold[s];
-                c.tick = grp * kG + s;
-                c.flags = 0; c.have = 0; c.obs_inc = 0.0; c.d_start = 0.0; c.end_term = 0.0;
-                h.prev[s] = -INFINITY; h.f[s] = 0.0; h.gchk[s] = INFINITY;
-#pragma unroll
-                for (int q = 0; q < 5; ++q) c.sums[q] = 0.0;
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) { h.x0[s][q] = NAN; c.cb[q] = c.cprev[q] = 0.0; c.bstar[q] = -1; }
-                off[s] = -1;
-                if (has_ticks && c.tick < p.n_ticks) {
-                    const TickGeom g = tick_geom_call(p, phase, c.tick);
-                    if (s == 0) base = g.i0;
-                    off[s] = g.i0 - base;
-                    if (g.n == 4) {
-                        c.flags |= kRegular;
-                        double ext = g.sampled;
-                        ext += (g.d_start < g.thr) ? g.d_start : g.avg / 2;
-                        ext += g.end_term;
-                        h.f[s] = ext / g.sampled;
-                        h.gchk[s] = (g.sampled / g.d_start) * (1.0 - 9.094947017729282e-13);   // 1 - 2^-40
-                        c.d_start = g.d_start;
-                        c.end_term = g.end_term;
-                    }
-                }
-            }
-            // A thread is self-regular if every tick it owns has a 4-sample window starting at an
-            // even sample; the window pattern (O1, O2) of such threads depends only on the phase.
-            bool self_ok = has_ticks && cold[0].tick < p.n_ticks && (cold[0].flags & kRegular) &&
-                           (base & 1) == 0 && base >= 0;
-            bool full_group = true;
-#pragma unroll
-            for (int s = 1; s < kG; ++s) {
-                if (has_ticks && cold[s].tick < p.n_ticks) { if (!(cold[s].flags & kRegular)) self_ok = false; }
-                else full_group = false;
-            }
-            int O1 = 0, O2 = 1;
-            {   // the warp adopts the pattern of its first self-regular lane with a full group
-                const unsigned cand = __ballot_sync(kFull, self_ok && full_group);
-                const int src = cand ? __ffs(cand) - 1 : 0;
-                O1 = __shfl_sync(kFull, off[1], src);
-                O2 = __shfl_sync(kFull, off[2], src);
-                if (!cand) { O1 = 0; O2 = 1; }
-            }
-            const bool pat_ok = (O1 == 0 && O2 == 1) || (O1 == 1 && O2 == 1) || (O1 == 1 && O2 == 2);
-            bool active = self_ok && pat_ok;
-#pragma unroll
-            for (int s = 1; s < kG; ++s)
-                if (has_ticks && cold[s].tick < p.n_ticks && off[s] != (s == 1 ? O1 : O2)) active = false;
-            if (!active) {
-                // neutral row code: loads stay inside the row, nothing is captured; the ticks
-                // (if any) are evaluated exactly by the whole warp afterwards
-                base = 0;
-#pragma unroll
-                for (int s = 0; s < kG; ++s) {
-                    h.f[s] = 0.0; h.gchk[s] = INFINITY;
-                    if (has_ticks && cold[s].tick < p.n_ticks) cold[s].flags |= kFallback;
-                }
-            } else {
-                // slots of a partial last group reuse tick 0's factors; their results are never read
-#pragma unroll
-                for (int s = 1; s < kG; ++s)
-                    if (!(cold[s].tick < p.n_ticks)) { h.f[s] = h.f[0]; h.gchk[s] = INFINITY; }
-            }
-            if (!pat_ok) { O1 = 0; O2 = 1; }
-
-            // ---- stream the rows
-            if (O1 == 0) consume_pv<T, NQ, 0, 1>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
-            else if (O2 == 1) consume_pv<T, NQ, 1, 1>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
-            else consume_pv<T, NQ, 1, 2>(a, ring, full_bar, empty_bar, it, base, h, cold, active, lane);
-
-            if (p.reserved & 2) return;   // (reserved bit 1: debugging aid, skip the per-tick finish)
-            // ---- finish each tick: histogram_quantile, ratios, validity
-#pragma unroll 1
-            for (int s = 0; s < kG; ++s) {
-                Cold<NQ>& t = cold[s];
-                v[s] = 0;
-                if (!(has_ticks && t.tick < p.n_ticks) || (t.flags & kFallback)) continue;
-                uint8_t valid = 0;
-                if (B > 0) {
-                    valid |= CG_V_QUANTILE;
-                    // observations after the monotonic fix; the search assumed the +Inf bucket itself
-                    const bool spec_ok = !(t.obs_inc < h.prev[s]);
-                    const double obs = t.obs_inc / range_s;
-                    const bool top_inf = isinf(s_le[B - 1]) && s_le[B - 1] > 0;
-                    for (int q = 0; q < p.n_q; ++q) {
-                        const double qq = p.q[q];
-                        double r;
-                        if (isnan(qq)) r = NAN;
-                        else if (qq < 0) r = -INFINITY;
-                        else if (qq > 1) r = INFINITY;
-                        else if (!top_inf || B < 2) r = NAN;
-                        else if (!spec_ok) { t.flags |= kFallback; r = NAN; }
-                        else if (obs == 0) r = NAN;
-                        else if (t.bstar[q] < 0) r = s_le[B - 2];
-                        else {
-                            const int bb = t.bstar[q];
-                            const double rank = qq * obs;
-                            const double cbr = t.cb[q] / range_s;
-                            const double cpr = bb > 0 ? t.cprev[q] / range_s : 0.0;
-                            // the search ran in increase space; confirm it in rate space
-                            if (!(cbr >= rank) || (bb > 0 && !(cpr < rank))) { t.flags |= kFallback; r = NAN; }
-                            else if (bb == 0 && s_le[0] <= 0) r = s_le[0];
-                            else {
-                                double start = 0.0, end = s_le[bb], cc = cbr, rk = rank;
-                                if (bb > 0) { start = s_le[bb - 1]; cc -= cpr; rk -= cpr; }
-                                r = start + (end - start) * (rk / cc);
-                            }
-                        }
-                        m[s][q] = r;
-                    }
-                }
-                const double total = t.sums[0], err = t.sums[1], lsum = t.sums[2], lcnt = t.sums[3], fb = t.sums[4];
-                const int nq = p.n_q;
-                m[s][nq + CG_M_ERROR_RESPONSES] = err;
-                if (total > 0) { m[s][nq + CG_M_ERROR_RATE] = err / total; valid |= CG_V_ERROR_RATE; }
-                else m[s][nq + CG_M_ERROR_RATE] = NAN;
-                if (lcnt > 0) { m[s][nq + CG_M_LATENCY_AVG] = lsum / lcnt; valid |= CG_V_LATENCY_AVG; }
-                else m[s][nq + CG_M_LATENCY_AVG] = NAN;
-                m[s][nq + CG_M_REQUEST_COUNT] = lcnt;
-                m[s][nq + CG_M_FEEDBACK_COUNT] = fb;
-                v[s] = valid;
-            }
-            // ---- exact re-evaluation of whatever the fast path could not decide
-#pragma unroll 1
-            for (int s = 0; s < kG; ++s) {
-                const bool need = has_ticks && cold[s].tick < p.n_ticks && (cold[s].flags & kFallback);
-                unsigned todo = __ballot_sync(kFull, need);
-                while (todo) {
-                    const int src = __ffs(todo) - 1;
-                    todo &= todo - 1;
-                    const int tk = __shfl_sync(kFull, cold[s].tick, src);
-                    double mm[CG_MAX_Q + CG_M_EXTRA];
-                    uint8_t vv;
-                    coop_eval_tick<T>(a, pv, phase, tk, lane, s_le, mm, vv);
-                    if (lane == src) {
-                        for (int c = 0; c < W; ++c) m[s][c] = mm[c];
-                        v[s] = vv;
-                    }
-                }
-            }
-    }
+__device__ __forceinline__ void row_increases_pat(const int pat, const T* __restrict__ row, const Hot<NQ>& h,
+                                                  const StreamArgs& a, const int32_t phase, const int tick0,
+                                                  double (&inc)[kG]) {
+    if (pat == 0) row_increases<T, NQ, 0, 1>(row, h, a, phase, tick0, inc);
+    else if (pat == 1) row_increases<T, NQ, 1, 1>(row, h, a, phase, tick0, inc);
+    else row_increases<T, NQ, 1, 2>(row, h, a, phase, tick0, inc);
 }
 
 template <typename T, int NQ, int CW>
 __global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 3 : 1)
 stream_kernel(const __grid_constant__ StreamArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
+    typedef Rec<NQ> R;
     const cg_params& p = a.p;
     unsigned char* ring = smem;
     double*   s_le   = reinterpret_cast<double*>(smem + a.off_le);
@@ -564,15 +332,34 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 
     // ===== consumers =====
     const int grp = tid;                       // thread <-> period of the tick grid
+    const int tick0 = grp * kG;
     const bool has_ticks = grp < a.n_groups;
-    const double range_s = (double)p.window_ms / 1000.0;
+    int n_mine = 0;                            // how many of the kG ticks exist
+    if (has_ticks) n_mine = min(kG, p.n_ticks - tick0);
+    double* rec = reinterpret_cast<double*>(smem + a.off_rec) + tid;          // field f at rec[f * n_cons]
+    int* rec_i = reinterpret_cast<int*>(reinterpret_cast<double*>(smem + a.off_rec) + (size_t)R::kInts * n_cons) + tid;
+#define CG_REC(f) rec[(f) * n_cons]
+#define CG_RECI(f) rec_i[(f) * n_cons]        // ints: [0, kG*NQ) bstar, kG*NQ valid bytes, kG*NQ+1 stash valid bytes
+    const int n_sc = (K + kRowsPerSlot - 1) / kRowsPerSlot;
+    const int pitch = p.row_pitch;
     uint32_t it = 0;
     int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
 
+    auto acquire = [&]() -> const T* {
+        const uint32_t slot = it % (uint32_t)a.n_slots;
+        mbar_wait(full_bar + slot, (it / (uint32_t)a.n_slots) & 1u);
+        return reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
+    };
+    auto release = [&]() {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_bar + (it % (uint32_t)a.n_slots));
+        ++it;
+    };
+
     for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
         const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
-        const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
         if (!hp) {
+            const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
             if (tid == 0) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
             if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = 0u;
             continue;
@@ -584,47 +371,268 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             uint32_t* nxt = s_bits + ((bit_buf + 1) % 3) * n_words;
             for (int w = tid; w < n_words; w += n_cons) nxt[w] = 0u;
         }
-        double nm[kG][3];          // the new version's gate inputs, kept for the old version's pass
-        uint8_t nv[kG];
-#pragma unroll
-        for (int s = 0; s < kG; ++s) { nm[s][0] = nm[s][1] = nm[s][2] = NAN; nv[s] = 0; }
-
+#pragma unroll 1
         for (int ver = 0; ver < 2; ++ver) {
             const int64_t pv = pair * 2 + ver;
-            double m[kG][CG_MAX_Q + CG_M_EXTRA];
-            uint8_t v[kG];
-#pragma unroll
-            for (int s = 0; s < kG; ++s) v[s] = 0;
-            run_version<T, NQ>(a, ring, full_bar, empty_bar, s_le, it, pv, grp, has_ticks, lane, m, v);
-            int tick_of[kG];
-#pragma unroll
-            for (int s = 0; s < kG; ++s) tick_of[s] = grp * kG + s;
-            // ---- outputs of this version; gate once both are known
+            const int32_t phase = a.phase[pv];
+            // ---- tick geometry of this thread (32-bit integers; every division is by a constant)
+            Hot<NQ> h;
+            int base = 0, off1 = -1, off2 = -1;
+            bool regular = n_mine > 0;
 #pragma unroll
             for (int s = 0; s < kG; ++s) {
-                const int tk = tick_of[s];
-                if (!(has_ticks && tk < p.n_ticks)) continue;
-                if (a.metrics) {
-                    double* o = a.metrics + ((size_t)pv * p.n_ticks + tk) * W;
-                    for (int c = 0; c < W; ++c) o[c] = m[s][c];
+                h.prev[s] = -INFINITY; h.f[s] = 0.0; h.gchk[s] = INFINITY;
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) h.x0[s][q] = NAN;
+                if (s < n_mine) {
+                    const int t = p.tick0_ms + (tick0 + s) * p.tick_step_ms, lo = t - p.window_ms;
+                    int i0 = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+                    int i1 = floor_div32(t - phase, p.period_ms);
+                    if (i0 < 0) i0 = 0;
+                    if (i1 > p.n_samples - 1) i1 = p.n_samples - 1;
+                    if (s == 0) base = i0;
+                    if (s == 1) off1 = i0 - base;
+                    if (s == 2) off2 = i0 - base;
+                    if (i1 - i0 + 1 == 4) {
+                        const double d_start = div_const((double)(phase + i0 * p.period_ms - lo), 1000.0, 1e-3);
+                        const double d_end = div_const((double)(t - (phase + i1 * p.period_ms)), 1000.0, 1e-3);
+                        double ext = a.sampled;
+                        ext += (d_start < a.thr) ? d_start : a.half_avg;
+                        ext += (d_end < a.thr) ? d_end : a.half_avg;
+                        h.f[s] = div_const(ext, a.sampled, a.rc_sampled);
+                        // an under-estimate of sampled/d_start only sends more rows to the exact path
+                        h.gchk[s] = (a.sampled * (double)__frcp_rd(__double2float_ru(d_start))) * (1.0 - 1e-6);
+                    } else regular = false;
                 }
-                if (a.valid) a.valid[(size_t)pv * p.n_ticks + tk] = v[s];
-                const double gm[3] = {p.n_q > 0 ? m[s][p.gate_q] : NAN, m[s][p.n_q + CG_M_ERROR_RATE],
-                                      m[s][p.n_q + CG_M_LATENCY_AVG]};
-                if (ver == 0) {
-                    nm[s][0] = gm[0]; nm[s][1] = gm[1]; nm[s][2] = gm[2]; nv[s] = v[s];
-                } else if (gate_eval(nm[s], nv[s], gm, v[s], p) & CG_G_PROMOTE) {
-                    atomicOr(bits + (tk >> 5), 1u << (tk & 31));
+            }
+            regular = regular && (base & 1) == 0 && base >= 0;
+            // the warp adopts the window pattern of its first regular lane that owns a full group
+            int pat = 0;
+            {
+                const unsigned cand = __ballot_sync(kFull, regular && n_mine == kG);
+                const int src = cand ? __ffs(cand) - 1 : 0;
+                const int O1 = __shfl_sync(kFull, off1, src), O2 = __shfl_sync(kFull, off2, src);
+                pat = (O1 == 0 && O2 == 1) ? 0 : (O1 == 1 && O2 == 1) ? 1 : (O1 == 1 && O2 == 2) ? 2 : -1;
+                if (!cand) pat = 0;
+                const int w1 = pat == 0 ? 0 : 1, w2 = pat == 2 ? 2 : 1;
+                if (pat < 0 || (n_mine > 1 && off1 != w1) || (n_mine > 2 && off2 != w2)) regular = false;
+                if (pat < 0) pat = 0;
+            }
+            const bool active = regular;
+            unsigned fb_mask = 0;                // ticks that need the exact warp-cooperative path
+            if (!active) {
+                // neutral row code: loads stay inside the row, nothing is captured
+                base = 0;
+                fb_mask = (1u << n_mine) - 1u;
+#pragma unroll
+                for (int s = 0; s < kG; ++s) { h.f[s] = 0.0; h.gchk[s] = INFINITY; }
+            } else {
+                // slots of a partial last group reuse tick 0's factors; their results are never read
+#pragma unroll
+                for (int s = 1; s < kG; ++s) if (s >= n_mine) { h.f[s] = h.f[0]; h.gchk[s] = INFINITY; }
+            }
+#pragma unroll
+            for (int q = 0; q < kG * NQ; ++q) CG_RECI(q) = -1;
+
+            // ---- scalar counter rows: sum(increase(...)) per role, in series order (:375-410)
+            {
+                double sums[kG][5];
+                unsigned have = 0;
+#pragma unroll
+                for (int s = 0; s < kG; ++s)
+#pragma unroll
+                    for (int q = 0; q < 5; ++q) sums[s][q] = 0.0;
+                for (int u = 0; u < n_sc; ++u) {
+                    const T* rows = acquire();
+                    const int k0 = u * kRowsPerSlot, nr = min(kRowsPerSlot, K - k0);
+                    if (!(p.reserved & 1))
+#pragma unroll 1
+                    for (int k = 0; k < nr; ++k) {
+                        double inc[kG];
+                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, inc);
+                        const unsigned role = p.scalar_role[k0 + k];
+#pragma unroll
+                        for (int q = 0; q < 5; ++q)
+                            if (role & (1u << q)) {
+#pragma unroll
+                                for (int s = 0; s < kG; ++s) sums[s][q] = (have & (1u << q)) ? sums[s][q] + inc[s] : inc[s];
+                                have |= 1u << q;
+                            }
+                    }
+                    release();
+                }
+                // derived metrics (:387-404), validity, optional record output
+                unsigned vbytes = 0;
+#pragma unroll
+                for (int s = 0; s < kG; ++s) {
+                    const double total = sums[s][0], err = sums[s][1], lsum = sums[s][2], lcnt = sums[s][3];
+                    unsigned valid = (B > 0) ? CG_V_QUANTILE : 0u;
+                    double er = NAN, avg = NAN;
+                    if (total > 0) { er = err / total; valid |= CG_V_ERROR_RATE; }
+                    if (lcnt > 0) { avg = lsum / lcnt; valid |= CG_V_LATENCY_AVG; }
+                    CG_REC(R::kEr + s) = er;
+                    CG_REC(R::kAvg + s) = avg;
+                    vbytes |= valid << (8 * s);
+                    if (a.metrics && s < n_mine && active) {
+                        double* o = a.metrics + ((size_t)pv * p.n_ticks + tick0 + s) * W + p.n_q;
+                        o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
+                        o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[s][4];
+                    }
+                }
+                CG_RECI(kG * NQ) = (int)vbytes;
+            }
+            if (B > 0) {
+                {   // ---- the +Inf bucket first: observations -> rank -> search threshold
+                    const T* rows = acquire();
+                    if (!(p.reserved & 1)) {
+                        double inc[kG];
+                        row_increases_pat<T, NQ>(pat, rows + base, h, a, phase, tick0, inc);
+#pragma unroll
+                        for (int s = 0; s < kG; ++s) {
+                            CG_REC(R::kObs + s) = inc[s];
+                            const double obs = div_const(inc[s], a.range_s, a.rc_range);
+#pragma unroll
+                            for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * a.range_s : NAN;
+                        }
+                    }
+                    release();
+                }
+                // ---- bucket rows 0..B-2: monotonic fix and the search for the rank, in bucket order
+                for (int b0 = 0; b0 < B - 1; b0 += kRowsPerSlot) {
+                    const T* rows = acquire();
+                    const int nr = min(kRowsPerSlot, B - 1 - b0);
+                    if (!(p.reserved & 1))
+#pragma unroll 1
+                    for (int k = 0; k < nr; ++k) {
+                        double inc[kG];
+                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, inc);
+                        double c[kG];
+                        bool any_hit = false;
+#pragma unroll
+                        for (int s = 0; s < kG; ++s) {
+                            c[s] = inc[s] < h.prev[s] ? h.prev[s] : inc[s];   // monotonic fix (Appendix A step 3)
+#pragma unroll
+                            for (int q = 0; q < NQ; ++q) any_hit |= c[s] >= h.x0[s][q];
+                        }
+                        if (__any_sync(kFull, any_hit)) {       // some lane's first bucket reaching the rank
+#pragma unroll
+                            for (int s = 0; s < kG; ++s)
+#pragma unroll
+                                for (int q = 0; q < NQ; ++q)
+                                    if (c[s] >= h.x0[s][q]) {
+                                        CG_RECI(s * NQ + q) = b0 + k;
+                                        CG_REC(R::kCb + s * NQ + q) = c[s];
+                                        CG_REC(R::kCprev + s * NQ + q) = h.prev[s];
+                                        h.x0[s][q] = NAN;       // never true again
+                                    }
+                        }
+#pragma unroll
+                        for (int s = 0; s < kG; ++s) h.prev[s] = c[s];
+                    }
+                    release();
+                }
+            }
+            if (p.reserved & 2) continue;   // (reserved bit 1: debugging aid, skip the per-tick finish)
+
+            // ---- finish each tick: histogram_quantile (Appendix A) from the captured search state
+            if (B > 0 && active) {
+                const bool top_inf = isinf(s_le[B - 1]) && s_le[B - 1] > 0;
+#pragma unroll
+                for (int s = 0; s < kG; ++s) {
+                    if (s >= n_mine) continue;
+                    const double obs_inc = CG_REC(R::kObs + s);
+                    // observations after the monotonic fix; the search assumed the +Inf bucket itself
+                    const bool spec_ok = !(obs_inc < h.prev[s]);
+                    const double obs = div_const(obs_inc, a.range_s, a.rc_range);
+                    for (int q = 0; q < p.n_q; ++q) {
+                        const double qq = p.q[q];
+                        double r;
+                        if (isnan(qq)) r = NAN;
+                        else if (qq < 0) r = -INFINITY;
+                        else if (qq > 1) r = INFINITY;
+                        else if (!top_inf || B < 2) r = NAN;
+                        else if (!spec_ok) { fb_mask |= 1u << s; r = NAN; }
+                        else if (obs == 0) r = NAN;
+                        else if (CG_RECI(s * NQ + q) < 0) r = s_le[B - 2];
+                        else {
+                            const int bb = CG_RECI(s * NQ + q);
+                            const double rank = qq * obs;
+                            const double cbr = div_const(CG_REC(R::kCb + s * NQ + q), a.range_s, a.rc_range);
+                            const double cpr = bb > 0 ? div_const(CG_REC(R::kCprev + s * NQ + q), a.range_s, a.rc_range) : 0.0;
+                            // the search ran in increase space; confirm it in rate space
+                            if (!(cbr >= rank) || (bb > 0 && !(cpr < rank))) { fb_mask |= 1u << s; r = NAN; }
+                            else if (bb == 0 && s_le[0] <= 0) r = s_le[0];
+                            else {
+                                double start = 0.0, end = s_le[bb], cc = cbr, rk = rank;
+                                if (bb > 0) { start = s_le[bb - 1]; cc -= cpr; rk -= cpr; }
+                                r = start + (end - start) * (rk / cc);
+                            }
+                        }
+                        if (q == p.gate_q) CG_REC(R::kQv + s) = r;
+                        if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick0 + s) * W + q] = r;
+                    }
+                }
+            }
+            if (a.valid && active)
+                for (int s = 0; s < n_mine; ++s)
+                    a.valid[(size_t)pv * p.n_ticks + tick0 + s] = (uint8_t)((CG_RECI(kG * NQ) >> (8 * s)) & 0xff);
+            // ---- exact re-evaluation of whatever the fast path could not decide
+#pragma unroll 1
+            for (int s = 0; s < kG; ++s) {
+                unsigned todo = __ballot_sync(kFull, (fb_mask >> s) & 1u);
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int tk = __shfl_sync(kFull, tick0 + s, src);
+                    double mm[CG_MAX_Q + CG_M_EXTRA];
+                    uint8_t vv;
+                    coop_eval_tick<T>(a, pv, phase, tk, lane, s_le, mm, vv);
+                    if (lane == src) {
+                        CG_REC(R::kQv + s) = p.n_q > 0 ? mm[p.gate_q] : NAN;
+                        CG_REC(R::kEr + s) = mm[p.n_q + CG_M_ERROR_RATE];
+                        CG_REC(R::kAvg + s) = mm[p.n_q + CG_M_LATENCY_AVG];
+                        CG_RECI(kG * NQ) = (CG_RECI(kG * NQ) & ~(0xff << (8 * s))) | ((int)vv << (8 * s));
+                        if (a.metrics) {
+                            double* o = a.metrics + ((size_t)pv * p.n_ticks + tk) * W;
+                            for (int c = 0; c < W; ++c) o[c] = mm[c];
+                        }
+                        if (a.valid) a.valid[(size_t)pv * p.n_ticks + tk] = vv;
+                    }
+                }
+            }
+            // ---- the new version's gate inputs wait for the old version's pass; then the gate
+            if (ver == 0) {
+#pragma unroll
+                for (int s = 0; s < kG; ++s) {
+                    CG_REC(R::kStash + s * 3 + 0) = (p.n_q > 0) ? CG_REC(R::kQv + s) : NAN;
+                    CG_REC(R::kStash + s * 3 + 1) = CG_REC(R::kEr + s);
+                    CG_REC(R::kStash + s * 3 + 2) = CG_REC(R::kAvg + s);
+                }
+                CG_RECI(kG * NQ + 1) = CG_RECI(kG * NQ);
+            } else {
+                const int nvb = CG_RECI(kG * NQ + 1), ovb = CG_RECI(kG * NQ);
+#pragma unroll
+                for (int s = 0; s < kG; ++s) {
+                    if (s >= n_mine) continue;
+                    const int tk = tick0 + s;
+                    const double nm[3] = {CG_REC(R::kStash + s * 3 + 0), CG_REC(R::kStash + s * 3 + 1), CG_REC(R::kStash + s * 3 + 2)};
+                    const double om[3] = {(p.n_q > 0) ? CG_REC(R::kQv + s) : NAN, CG_REC(R::kEr + s), CG_REC(R::kAvg + s)};
+                    if (gate_eval(nm, (uint8_t)((nvb >> (8 * s)) & 0xff), om, (uint8_t)((ovb >> (8 * s)) & 0xff), p) & CG_G_PROMOTE)
+                        atomicOr(bits + (tk >> 5), 1u << (tk & 31));
                 }
             }
         }
         // ---- all consumer threads have OR-ed their gate bits: replay the step loop
         asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
         if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = bits[w];
-        if (tid == 0)
+        if (tid == 0) {
+            const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
             a.decisions[pair] = replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, true, st_tick, p);
+        }
         bit_buf = (bit_buf + 1) % 3;
     }
+#undef CG_REC
+#undef CG_RECI
 }
 
 // Host-side launcher for one (element type, quantile count) instance; CW is picked at run time.
