@@ -30,8 +30,10 @@ def _units():
     for tname, tchar in (("double", "d"), ("float", "f")):
         for nq in (1, 2, 3, 4):
             name = f"cg_launch_stream_{tchar}{nq}"
-            units.append((name, "cg_stream_inst.cu",
-                          [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]))
+            defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]
+            if os.environ.get("CG_TIMING") and name == "cg_launch_stream_d1":
+                defs += ["-DCG_TIMING", "-DCG_TIMING_EXPORT"]    # developer aid: in-kernel phase timers
+            units.append((name, "cg_stream_inst.cu", defs))
     return units
 
 

@@ -180,12 +180,12 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
     const int threads = a.consumer_warps * 32 + 32;
     int per_sm = 1, slots = 0;
-    for (int c = (a.consumer_warps <= 4 ? 3 : 1); c >= 1; --c) {
+    for (int c = (a.consumer_warps <= 4 ? 4 : 1); c >= 1; --c) {
         if (c * threads > 2048) continue;
         const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
         if (budget <= fixed) continue;
         const int sl = (int)((budget - fixed) / a.slot_bytes);
-        if (sl >= 6 || (c == 1 && sl >= 3)) { per_sm = c; slots = sl; break; }
+        if (sl >= 3) { per_sm = c; slots = sl; break; }
         if (sl >= 3 && slots == 0) { per_sm = c; slots = sl; }
     }
     if (slots < 3) return fail(CG_EINVAL, "streaming kernel: ring does not fit shared memory");

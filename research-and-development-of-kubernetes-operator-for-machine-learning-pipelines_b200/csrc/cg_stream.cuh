@@ -33,6 +33,16 @@ constexpr int kRowsPerSlot = 4;
 constexpr int kG = 3;            // ticks per thread (one period of the tick grid)
 constexpr unsigned kFull = 0xffffffffu;
 
+// developer aid (build with CG_TIMING=1): per-phase warp-cycle counters, read by tools/profile_kernel.py
+#ifdef CG_TIMING
+__device__ unsigned long long cg_timing[16];   // wait, rows, setup, finish, barrier, total, warps, long waits
+#define CG_T(var) const long long var = clock64()
+#define CG_TADD(i, d) do { if (lane == 0) atomicAdd(&cg_timing[i], (unsigned long long)(d)); } while (0)
+#else
+#define CG_T(var)
+#define CG_TADD(i, d)
+#endif
+
 struct StreamArgs {
     const void*    scalars;
     const void*    buckets;
@@ -237,13 +247,16 @@ static __device__ __noinline__ double slow_increase(const StreamArgs& a, int32_t
 // (1,1), (1,2) and depend only on the series phase.  All 32 lanes call this.
 template <typename T, int NQ, int O1, int O2>
 __device__ __forceinline__ void row_increases(const T* __restrict__ row, const Hot<NQ>& h, const StreamArgs& a,
-                                              const int32_t phase, const int tick0, double (&inc)[kG]) {
+                                              const int32_t phase, const int tick0, const unsigned live,
+                                              double (&inc)[kG]) {
     double x[6];
     Tile6<T>::load(row, x);
     double w0 = x[3] - x[0], w1 = x[4] - x[1], w2 = (O2 == 2) ? x[5] - x[2] : 0.0;
     const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3],
                r5 = (O2 == 2) && x[5] < x[4];
-    if (__any_sync(kFull, r1 | r2 | r3 | r4 | r5)) {   // counter resets are rare (Appendix A step 2)
+    // `live`: bit s set when tick s of this thread is evaluated by the fast path; lanes and tick
+    // slots that are not (idle lanes, a partial last group) must never drag the warp into a rare path
+    if (__any_sync(kFull, (r1 | r2 | r3 | r4 | r5) && live)) {   // counter resets are rare (Appendix A step 2)
         if (r1) w0 += x[0];
         if (r2) { w0 += x[1]; w1 += x[1]; }
         if (r3) { w0 += x[2]; w1 += x[2]; if (O2 == 2) w2 += x[2]; }
@@ -255,7 +268,7 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
     bool slow[kG];
 #pragma unroll
     for (int s = 0; s < kG; ++s) {
-        slow[s] = !(fst[s] * h.gchk[s] >= res[s]);
+        slow[s] = !(fst[s] * h.gchk[s] >= res[s]) && ((live >> s) & 1u);
         inc[s] = res[s] * h.f[s];
     }
     if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   // rare: the zero-point clamp may fire
@@ -268,14 +281,14 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
 template <typename T, int NQ>
 __device__ __forceinline__ void row_increases_pat(const int pat, const T* __restrict__ row, const Hot<NQ>& h,
                                                   const StreamArgs& a, const int32_t phase, const int tick0,
-                                                  double (&inc)[kG]) {
-    if (pat == 0) row_increases<T, NQ, 0, 1>(row, h, a, phase, tick0, inc);
-    else if (pat == 1) row_increases<T, NQ, 1, 1>(row, h, a, phase, tick0, inc);
-    else row_increases<T, NQ, 1, 2>(row, h, a, phase, tick0, inc);
+                                                  const unsigned live, double (&inc)[kG]) {
+    if (pat == 0) row_increases<T, NQ, 0, 1>(row, h, a, phase, tick0, live, inc);
+    else if (pat == 1) row_increases<T, NQ, 1, 1>(row, h, a, phase, tick0, live, inc);
+    else row_increases<T, NQ, 1, 2>(row, h, a, phase, tick0, live, inc);
 }
 
 template <typename T, int NQ, int CW>
-__global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 3 : 1)
+__global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 4 : 1)
 stream_kernel(const __grid_constant__ StreamArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     typedef Rec<NQ> R;
@@ -302,27 +315,47 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 
     if (warp == a.consumer_warps) {
         // ===== producer: one elected lane drives the TMA bulk-copy engine =====
+        // This lane is on the critical path of the whole CTA (its instructions issue as slowly as
+        // any other warp's), so the per-push work is kept to a handful of instructions.
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t slot = 0, par = 1;        // ring position; parity to wait for on empty[slot]
+            const uint32_t n_slots = (uint32_t)a.n_slots, slot_bytes = a.slot_bytes;
+            const uint32_t ring_s = smem_u32(ring), full_s = smem_u32(full_bar), empty_s = smem_u32(empty_bar);
             auto push = [&](const char* src, uint32_t bytes) {
-                const uint32_t slot = it % (uint32_t)a.n_slots;
-                mbar_wait_backoff(empty_bar + slot, ((it / (uint32_t)a.n_slots) & 1u) ^ 1u);
-                mbar_arrive_expect_tx(full_bar + slot, bytes);
-                bulk_g2s(ring + (size_t)slot * a.slot_bytes, src, bytes, full_bar + slot);
-                ++it;
+                const uint32_t eb = empty_s + slot * 8u, fb = full_s + slot * 8u;
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\t"
+                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                    "@p bra DONE_%=;\n\t"
+                    "WAIT_%=:\n\t"
+                    "nanosleep.u32 96;\n\t"      // yield the scheduler to the consumer warps
+                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                    "@!p bra WAIT_%=;\n\t"
+                    "DONE_%=:\n\t"
+                    "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n\t"
+                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%4], [%5], %3, [%2];\n\t"
+                    "}" ::"r"(eb), "r"(par), "r"(fb), "r"(bytes), "r"(ring_s + slot * slot_bytes), "l"(src)
+                    : "memory");
+                if (++slot == n_slots) { slot = 0; par ^= 1u; }
             };
+            const uint32_t rb = (uint32_t)row_bytes;
+            const uint32_t full_slot = (uint32_t)kRowsPerSlot * rb;
             for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
                 if (a.has_previous && !a.has_previous[pair]) continue;
+                const char* gs = reinterpret_cast<const char*>(a.scalars) + (size_t)pair * 2 * K * row_bytes;
+                const char* gb = reinterpret_cast<const char*>(a.buckets) + (size_t)pair * 2 * B * row_bytes;
+#pragma unroll 1
                 for (int ver = 0; ver < 2; ++ver) {
-                    const int64_t pv = pair * 2 + ver;
-                    const char* gs = reinterpret_cast<const char*>(a.scalars) + (size_t)pv * K * row_bytes;
-                    const char* gb = reinterpret_cast<const char*>(a.buckets) + (size_t)pv * B * row_bytes;
-                    for (int k0 = 0; k0 < K; k0 += kRowsPerSlot)
-                        push(gs + (size_t)k0 * row_bytes, (uint32_t)(min(kRowsPerSlot, K - k0) * row_bytes));
+                    int k = K;
+                    for (; k > kRowsPerSlot; k -= kRowsPerSlot, gs += full_slot) push(gs, full_slot);
+                    if (k > 0) { push(gs, (uint32_t)k * rb); gs += (size_t)k * rb; }
                     if (B > 0) {
-                        push(gb + (size_t)(B - 1) * row_bytes, (uint32_t)row_bytes);
-                        for (int b0 = 0; b0 < B - 1; b0 += kRowsPerSlot)
-                            push(gb + (size_t)b0 * row_bytes, (uint32_t)(min(kRowsPerSlot, B - 1 - b0) * row_bytes));
+                        push(gb + (size_t)(B - 1) * rb, rb);
+                        int b = B - 1;
+                        const char* src = gb;
+                        for (; b > kRowsPerSlot; b -= kRowsPerSlot, src += full_slot) push(src, full_slot);
+                        if (b > 0) push(src, (uint32_t)b * rb);
+                        gb += (size_t)B * rb;
                     }
                 }
             }
@@ -345,16 +378,28 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
     uint32_t it = 0;
     int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
 
+#ifdef CG_TIMING
+    long long t_acq = 0;
+#endif
     auto acquire = [&]() -> const T* {
         const uint32_t slot = it % (uint32_t)a.n_slots;
+        CG_T(tw0);
         mbar_wait(full_bar + slot, (it / (uint32_t)a.n_slots) & 1u);
+#ifdef CG_TIMING
+        t_acq = clock64();
+        CG_TADD(0, t_acq - tw0);
+#endif
         return reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
     };
     auto release = [&]() {
         __syncwarp();
+#ifdef CG_TIMING
+        CG_TADD(1, clock64() - t_acq);
+#endif
         if (lane == 0) mbar_arrive(empty_bar + (it % (uint32_t)a.n_slots));
         ++it;
     };
+    CG_T(tk0);
 
     for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
         const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
@@ -375,6 +420,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         for (int ver = 0; ver < 2; ++ver) {
             const int64_t pv = pair * 2 + ver;
             const int32_t phase = a.phase[pv];
+            CG_T(ts0);
             // ---- tick geometry of this thread (32-bit integers; every division is by a constant)
             Hot<NQ> h;
             int base = 0, off1 = -1, off2 = -1;
@@ -431,9 +477,11 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll
                 for (int s = 1; s < kG; ++s) if (s >= n_mine) { h.f[s] = h.f[0]; h.gchk[s] = INFINITY; }
             }
+            const unsigned live = active ? (1u << n_mine) - 1u : 0u;   // ticks the fast path evaluates
 #pragma unroll
             for (int q = 0; q < kG * NQ; ++q) CG_RECI(q) = -1;
 
+            CG_TADD(2, clock64() - ts0);
             // ---- scalar counter rows: sum(increase(...)) per role, in series order (:375-410)
             {
                 double sums[kG][5];
@@ -449,7 +497,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll 1
                     for (int k = 0; k < nr; ++k) {
                         double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, inc);
+                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, live, inc);
                         const unsigned role = p.scalar_role[k0 + k];
 #pragma unroll
                         for (int q = 0; q < 5; ++q)
@@ -486,7 +534,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     const T* rows = acquire();
                     if (!(p.reserved & 1)) {
                         double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + base, h, a, phase, tick0, inc);
+                        row_increases_pat<T, NQ>(pat, rows + base, h, a, phase, tick0, live, inc);
 #pragma unroll
                         for (int s = 0; s < kG; ++s) {
                             CG_REC(R::kObs + s) = inc[s];
@@ -505,7 +553,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll 1
                     for (int k = 0; k < nr; ++k) {
                         double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, inc);
+                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, live, inc);
                         double c[kG];
                         bool any_hit = false;
 #pragma unroll
@@ -533,7 +581,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                 }
             }
             if (p.reserved & 2) continue;   // (reserved bit 1: debugging aid, skip the per-tick finish)
-
+            CG_T(tf0);
             // ---- finish each tick: histogram_quantile (Appendix A) from the captured search state
             if (B > 0 && active) {
                 const bool top_inf = isinf(s_le[B - 1]) && s_le[B - 1] > 0;
@@ -576,11 +624,14 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             if (a.valid && active)
                 for (int s = 0; s < n_mine; ++s)
                     a.valid[(size_t)pv * p.n_ticks + tick0 + s] = (uint8_t)((CG_RECI(kG * NQ) >> (8 * s)) & 0xff);
+            CG_T(tq1);
+            CG_TADD(8, tq1 - tf0);
             // ---- exact re-evaluation of whatever the fast path could not decide
 #pragma unroll 1
             for (int s = 0; s < kG; ++s) {
                 unsigned todo = __ballot_sync(kFull, (fb_mask >> s) & 1u);
                 while (todo) {
+                    CG_TADD(7, 1);
                     const int src = __ffs(todo) - 1;
                     todo &= todo - 1;
                     const int tk = __shfl_sync(kFull, tick0 + s, src);
@@ -600,6 +651,8 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     }
                 }
             }
+            CG_T(tq2);
+            CG_TADD(9, tq2 - tq1);
             // ---- the new version's gate inputs wait for the old version's pass; then the gate
             if (ver == 0) {
 #pragma unroll
@@ -621,9 +674,12 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         atomicOr(bits + (tk >> 5), 1u << (tk & 31));
                 }
             }
+            CG_TADD(3, clock64() - tf0);
         }
         // ---- all consumer threads have OR-ed their gate bits: replay the step loop
+        CG_T(tb0);
         asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
+        CG_TADD(4, clock64() - tb0);
         if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = bits[w];
         if (tid == 0) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
@@ -631,6 +687,10 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         }
         bit_buf = (bit_buf + 1) % 3;
     }
+#ifdef CG_TIMING
+    CG_TADD(5, clock64() - tk0);
+    CG_TADD(6, 1);
+#endif
 #undef CG_REC
 #undef CG_RECI
 }

@@ -7,3 +7,11 @@
 cudaError_t CG_INST_NAME(const cg::StreamArgs& a, int grid, int block, int cw_template, cudaStream_t s) {
     return cg::launch_stream_tn<CG_INST_T, CG_INST_NQ>(a, grid, block, cw_template, s);
 }
+
+#if defined(CG_TIMING) && defined(CG_TIMING_EXPORT)
+extern "C" int cg_debug_timing(unsigned long long* out8, int reset) {
+    if (cudaMemcpyFromSymbol(out8, cg::cg_timing, sizeof(unsigned long long) * 16) != cudaSuccess) return 1;
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(cg::cg_timing, z, sizeof(z)); }
+    return 0;
+}
+#endif

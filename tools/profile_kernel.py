@@ -26,3 +26,13 @@ torch.cuda.synchronize()
 ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(reps)]
 gb = n * p.bytes_per_pair() / 1e9
 print(f"pairs={n} path={path} ms={['%.3f' % m for m in ms]} GB/s={gb / (min(ms) * 1e-3):.1f} states={torch.bincount(dec[:, 2], minlength=4).tolist()}")
+
+if os.environ.get("CG_TIMING"):
+    import ctypes as C
+    from canary_b200 import _lib
+    buf = (C.c_ulonglong * 16)()
+    _lib.lib.cg_debug_timing(buf, 1)
+    names = ["wait_full", "rows", "setup", "finish", "barrier", "total", "warps", "coop_calls", "finish_quantile", "finish_fallback", "-", "-", "-", "-", "-", "-"]
+    vals = list(buf)
+    tot = vals[5] or 1
+    print("warp-cycles over all launches:", {n: f"{v:.3e} ({100 * v / tot:.1f}%)" for n, v in zip(names, vals)})
