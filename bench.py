@@ -316,7 +316,9 @@ def main():
             "series_samples_per_sec": value * 2 * (p.n_scalar + p.n_buckets) * p.n_samples,
             "kernel_ms": kern_ms,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None if traffic is None else traffic.get("bytes_per_launch"),
+                         "frac": achieved / peak,
+                         "traffic": None if traffic is None else traffic["bytes_per_pair"] * n,
+                         "traffic_source": None if traffic is None else traffic["source"] + "; scaled per pair",
                          "peak_source": peak_src, "kernel": "cg_eval_fused",
                          "algorithmic_bytes_per_launch": n * bytes_per_pair},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
