@@ -194,7 +194,7 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     a.n_slots = slots;
     size_t off = (size_t)slots * a.slot_bytes;
     a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
-    a.off_bits = (uint32_t)off; off += 3 * n_words * 4;
+    a.off_bits = (uint32_t)off; off += 3 * n_words * 4 + 16;
     off = (off + 7) & ~(size_t)7;
     a.off_bars = (uint32_t)off; off += (size_t)2 * slots * 8;
     a.off_rec = (uint32_t)off; off += rec;

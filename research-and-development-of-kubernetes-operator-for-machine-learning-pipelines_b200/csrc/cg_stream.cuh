@@ -308,7 +308,8 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         mbar_init_fence();
     }
     for (int b = tid; b < B; b += blockDim.x) s_le[b] = a.le[b];
-    for (int w = tid; w < 3 * n_words; w += blockDim.x) s_bits[w] = 0u;
+    uint32_t* s_cnt = s_bits + 3 * n_words;     // arrival counters, one per gate-bit buffer
+    for (int w = tid; w < 3 * n_words + 3; w += blockDim.x) s_bits[w] = 0u;
     __syncthreads();
 
     const size_t row_bytes = (size_t)p.row_pitch * sizeof(T);
@@ -415,67 +416,63 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             // reader is left; the next pair's atomicOr comes after this pair's barrier.
             uint32_t* nxt = s_bits + ((bit_buf + 1) % 3) * n_words;
             for (int w = tid; w < n_words; w += n_cons) nxt[w] = 0u;
+            if (tid == 0) s_cnt[(bit_buf + 1) % 3] = 0u;
         }
 #pragma unroll 1
         for (int ver = 0; ver < 2; ++ver) {
             const int64_t pv = pair * 2 + ver;
             const int32_t phase = a.phase[pv];
             CG_T(ts0);
-            // ---- tick geometry of this thread (32-bit integers; every division is by a constant)
+            // ---- tick geometry.  Three tick steps are exactly two scrape periods, so the window of
+            // tick 3g+s is the window of tick s shifted by 2g samples and its extrapolation terms
+            // (d_start, d_end -> f, gchk) depend on s alone: lanes 0..2 compute them once per
+            // (pair, version) and the warp shares them.  32-bit integers throughout (the eligibility
+            // test bounds every time stamp); every division is by a constant (div_const).
             Hot<NQ> h;
-            int base = 0, off1 = -1, off2 = -1;
-            bool regular = n_mine > 0;
-#pragma unroll
-            for (int s = 0; s < kG; ++s) {
-                h.prev[s] = -INFINITY; h.f[s] = 0.0; h.gchk[s] = INFINITY;
-#pragma unroll
-                for (int q = 0; q < NQ; ++q) h.x0[s][q] = NAN;
-                if (s < n_mine) {
-                    const int t = p.tick0_ms + (tick0 + s) * p.tick_step_ms, lo = t - p.window_ms;
-                    int i0 = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
-                    int i1 = floor_div32(t - phase, p.period_ms);
-                    if (i0 < 0) i0 = 0;
-                    if (i1 > p.n_samples - 1) i1 = p.n_samples - 1;
-                    if (s == 0) base = i0;
-                    if (s == 1) off1 = i0 - base;
-                    if (s == 2) off2 = i0 - base;
-                    if (i1 - i0 + 1 == 4) {
-                        const double d_start = div_const((double)(phase + i0 * p.period_ms - lo), 1000.0, 1e-3);
-                        const double d_end = div_const((double)(t - (phase + i1 * p.period_ms)), 1000.0, 1e-3);
-                        double ext = a.sampled;
-                        ext += (d_start < a.thr) ? d_start : a.half_avg;
-                        ext += (d_end < a.thr) ? d_end : a.half_avg;
-                        h.f[s] = div_const(ext, a.sampled, a.rc_sampled);
-                        // an under-estimate of sampled/d_start only sends more rows to the exact path
-                        h.gchk[s] = (a.sampled * (double)__frcp_rd(__double2float_ru(d_start))) * (1.0 - 1e-6);
-                    } else regular = false;
+            int i0r = 0, i1r = 0;            // unclamped window bounds of tick s = lane (lanes 0..2)
+            double fs = 0.0, gs = INFINITY;
+            if (lane < kG) {
+                const int t = p.tick0_ms + lane * p.tick_step_ms, lo = t - p.window_ms;
+                i0r = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+                i1r = floor_div32(t - phase, p.period_ms);
+                if (i1r - i0r + 1 == 4) {
+                    const double d_start = div_const((double)(phase + i0r * p.period_ms - lo), 1000.0, 1e-3);
+                    const double d_end = div_const((double)(t - (phase + i1r * p.period_ms)), 1000.0, 1e-3);
+                    double ext = a.sampled;
+                    ext += (d_start < a.thr) ? d_start : a.half_avg;
+                    ext += (d_end < a.thr) ? d_end : a.half_avg;
+                    fs = div_const(ext, a.sampled, a.rc_sampled);
+                    // an under-estimate of sampled/d_start only sends more rows to the exact path
+                    gs = (a.sampled * (double)__frcp_rd(__double2float_ru(d_start))) * (1.0 - 1e-6);
                 }
             }
-            regular = regular && (base & 1) == 0 && base >= 0;
-            // the warp adopts the window pattern of its first regular lane that owns a full group
-            int pat = 0;
-            {
-                const unsigned cand = __ballot_sync(kFull, regular && n_mine == kG);
-                const int src = cand ? __ffs(cand) - 1 : 0;
-                const int O1 = __shfl_sync(kFull, off1, src), O2 = __shfl_sync(kFull, off2, src);
-                pat = (O1 == 0 && O2 == 1) ? 0 : (O1 == 1 && O2 == 1) ? 1 : (O1 == 1 && O2 == 2) ? 2 : -1;
-                if (!cand) pat = 0;
-                const int w1 = pat == 0 ? 0 : 1, w2 = pat == 2 ? 2 : 1;
-                if (pat < 0 || (n_mine > 1 && off1 != w1) || (n_mine > 2 && off2 != w2)) regular = false;
-                if (pat < 0) pat = 0;
+            int i0s[kG], i1s[kG];
+#pragma unroll
+            for (int s = 0; s < kG; ++s) {
+                i0s[s] = __shfl_sync(kFull, i0r, s);
+                i1s[s] = __shfl_sync(kFull, i1r, s);
+                h.f[s] = __shfl_sync(kFull, fs, s);
+                h.gchk[s] = __shfl_sync(kFull, gs, s);
+                h.prev[s] = -INFINITY;
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) h.x0[s][q] = NAN;
             }
+            const int off1 = i0s[1] - i0s[0], off2 = i0s[2] - i0s[0];
+            int pat = (off1 == 0 && off2 == 1) ? 0 : (off1 == 1 && off2 == 1) ? 1 : (off1 == 1 && off2 == 2) ? 2 : -1;
+            int base = i0s[0] + 2 * grp;
+            // this thread's ticks are regular if each has an unclipped 4-sample window
+            bool regular = n_mine > 0 && pat >= 0 && (base & 1) == 0;
+#pragma unroll
+            for (int s = 0; s < kG; ++s)
+                if (s < n_mine && !(i1s[s] - i0s[s] + 1 == 4 && i0s[s] + 2 * grp >= 0 && i1s[s] + 2 * grp <= p.n_samples - 1))
+                    regular = false;
+            if (pat < 0) pat = 0;
             const bool active = regular;
             unsigned fb_mask = 0;                // ticks that need the exact warp-cooperative path
             if (!active) {
                 // neutral row code: loads stay inside the row, nothing is captured
                 base = 0;
                 fb_mask = (1u << n_mine) - 1u;
-#pragma unroll
-                for (int s = 0; s < kG; ++s) { h.f[s] = 0.0; h.gchk[s] = INFINITY; }
-            } else {
-                // slots of a partial last group reuse tick 0's factors; their results are never read
-#pragma unroll
-                for (int s = 1; s < kG; ++s) if (s >= n_mine) { h.f[s] = h.f[0]; h.gchk[s] = INFINITY; }
             }
             const unsigned live = active ? (1u << n_mine) - 1u : 0u;   // ticks the fast path evaluates
 #pragma unroll
@@ -676,14 +673,23 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             }
             CG_TADD(3, clock64() - tf0);
         }
-        // ---- all consumer threads have OR-ed their gate bits: replay the step loop
-        CG_T(tb0);
-        asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
-        CG_TADD(4, clock64() - tb0);
-        if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = bits[w];
-        if (tid == 0) {
-            const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
-            a.decisions[pair] = replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, true, st_tick, p);
+        // ---- the warp that finishes this pair last replays the step loop; nobody waits.
+        // (Consumer warps of a CTA are never more than the ring depth apart, far less than a pair,
+        // so the triple-buffered gate bits and arrival counters cannot be overtaken.)
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            last = (atomicAdd(s_cnt + bit_buf, 1u) == (unsigned)a.consumer_warps - 1u) ? 1 : 0;
+        }
+        last = __shfl_sync(kFull, last, 0);
+        if (last) {
+            __threadfence_block();
+            if (a.gate_bits) for (int w = lane; w < n_words; w += 32) a.gate_bits[pair * n_words + w] = bits[w];
+            if (lane == 0) {
+                const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
+                a.decisions[pair] = replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, true, st_tick, p);
+            }
         }
         bit_buf = (bit_buf + 1) % 3;
     }
