@@ -178,7 +178,7 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
-    const int threads = a.consumer_warps * 32 + 32;
+    const int threads = a.consumer_warps * 32;
     int per_sm = 1, slots = 0;
     for (int c = (a.consumer_warps <= 4 ? 4 : 1); c >= 1; --c) {
         if (c * threads > 2048) continue;
@@ -196,7 +196,8 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
     a.off_bits = (uint32_t)off; off += 3 * n_words * 4 + 16;
     off = (off + 7) & ~(size_t)7;
-    a.off_bars = (uint32_t)off; off += (size_t)2 * slots * 8;
+    a.off_bars = (uint32_t)off; off += (size_t)slots * 8 + (size_t)slots * 4 + 8;
+    off = (off + 15) & ~(size_t)15;
     a.off_rec = (uint32_t)off; off += rec;
     a.smem_bytes = (uint32_t)off;
     plan->block = threads;

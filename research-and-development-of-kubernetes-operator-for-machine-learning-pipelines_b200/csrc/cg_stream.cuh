@@ -287,8 +287,14 @@ __device__ __forceinline__ void row_increases_pat(const int pat, const T* __rest
     else row_increases<T, NQ, 1, 2>(row, h, a, phase, tick0, live, inc);
 }
 
+// Position in a CTA's stream of ring fills: (pair, version, slot-use within the version).
+struct FillCursor {
+    int64_t pair;
+    int ver, u;
+};
+
 template <typename T, int NQ, int CW>
-__global__ void __launch_bounds__(CW * 32 + 32, (CW <= 4) ? 4 : 1)
+__global__ void __launch_bounds__(CW * 32, (CW <= 4) ? 4 : 1)
 stream_kernel(const __grid_constant__ StreamArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     typedef Rec<NQ> R;
@@ -296,72 +302,67 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
     unsigned char* ring = smem;
     double*   s_le   = reinterpret_cast<double*>(smem + a.off_le);
     uint32_t* s_bits = reinterpret_cast<uint32_t*>(smem + a.off_bits);
-    uint64_t* full_bar  = reinterpret_cast<uint64_t*>(smem + a.off_bars);
-    uint64_t* empty_bar = full_bar + a.n_slots;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + a.off_bars);
+    uint32_t* s_arr = reinterpret_cast<uint32_t*>(full_bar + a.n_slots);   // per-slot arrival counters
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int n_cons = a.consumer_warps * 32;
     const int K = p.n_scalar, B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
     const int n_words = (p.n_ticks + 31) >> 5;
+    uint32_t* s_cnt = s_bits + 3 * n_words;     // arrival counters, one per gate-bit buffer
     if (tid == 0) {
-        for (int s = 0; s < a.n_slots; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, a.consumer_warps); }
+        for (int s = 0; s < a.n_slots; ++s) { mbar_init(full_bar + s, 1); s_arr[s] = 0u; }
         mbar_init_fence();
     }
     for (int b = tid; b < B; b += blockDim.x) s_le[b] = a.le[b];
-    uint32_t* s_cnt = s_bits + 3 * n_words;     // arrival counters, one per gate-bit buffer
     for (int w = tid; w < 3 * n_words + 3; w += blockDim.x) s_bits[w] = 0u;
     __syncthreads();
 
     const size_t row_bytes = (size_t)p.row_pitch * sizeof(T);
+    const int n_sc = (K + kRowsPerSlot - 1) / kRowsPerSlot;
+    const int n_use = n_sc + (B > 0 ? 1 + (B - 1 + kRowsPerSlot - 1) / kRowsPerSlot : 0);
 
-    if (warp == a.consumer_warps) {
-        // ===== producer: one elected lane drives the TMA bulk-copy engine =====
-        // This lane is on the critical path of the whole CTA (its instructions issue as slowly as
-        // any other warp's), so the per-push work is kept to a handful of instructions.
-        if (lane == 0) {
-            uint32_t slot = 0, par = 1;        // ring position; parity to wait for on empty[slot]
-            const uint32_t n_slots = (uint32_t)a.n_slots, slot_bytes = a.slot_bytes;
-            const uint32_t ring_s = smem_u32(ring), full_s = smem_u32(full_bar), empty_s = smem_u32(empty_bar);
-            auto push = [&](const char* src, uint32_t bytes) {
-                const uint32_t eb = empty_s + slot * 8u, fb = full_s + slot * 8u;
-                asm volatile(
-                    "{\n\t.reg .pred p;\n\t"
-                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-                    "@p bra DONE_%=;\n\t"
-                    "WAIT_%=:\n\t"
-                    "nanosleep.u32 96;\n\t"      // yield the scheduler to the consumer warps
-                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-                    "@!p bra WAIT_%=;\n\t"
-                    "DONE_%=:\n\t"
-                    "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n\t"
-                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%4], [%5], %3, [%2];\n\t"
-                    "}" ::"r"(eb), "r"(par), "r"(fb), "r"(bytes), "r"(ring_s + slot * slot_bytes), "l"(src)
-                    : "memory");
-                if (++slot == n_slots) { slot = 0; par ^= 1u; }
-            };
-            const uint32_t rb = (uint32_t)row_bytes;
-            const uint32_t full_slot = (uint32_t)kRowsPerSlot * rb;
-            for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
-                if (a.has_previous && !a.has_previous[pair]) continue;
-                const char* gs = reinterpret_cast<const char*>(a.scalars) + (size_t)pair * 2 * K * row_bytes;
-                const char* gb = reinterpret_cast<const char*>(a.buckets) + (size_t)pair * 2 * B * row_bytes;
-#pragma unroll 1
-                for (int ver = 0; ver < 2; ++ver) {
-                    int k = K;
-                    for (; k > kRowsPerSlot; k -= kRowsPerSlot, gs += full_slot) push(gs, full_slot);
-                    if (k > 0) { push(gs, (uint32_t)k * rb); gs += (size_t)k * rb; }
-                    if (B > 0) {
-                        push(gb + (size_t)(B - 1) * rb, rb);
-                        int b = B - 1;
-                        const char* src = gb;
-                        for (; b > kRowsPerSlot; b -= kRowsPerSlot, src += full_slot) push(src, full_slot);
-                        if (b > 0) push(src, (uint32_t)b * rb);
-                        gb += (size_t)B * rb;
-                    }
-                }
-            }
+    // ---- the ring is refilled by the consumers themselves: the warp that releases a slot last
+    // issues the TMA bulk copy of the fill that comes n_slots later in the stream.  No producer
+    // warp, no polling on "empty" barriers.  Order per (pair, version): the K scalar rows, the
+    // +Inf bucket row, then bucket rows 0..B-2 in groups of kRowsPerSlot; every sample leaves
+    // HBM exactly once.
+    auto cursor_valid = [&](const FillCursor& c) { return c.pair < a.n_pairs; };
+    auto skip_pairs = [&](FillCursor& c) {
+        while (c.pair < a.n_pairs && a.has_previous && !a.has_previous[c.pair]) c.pair += gridDim.x;
+    };
+    auto cursor_next = [&](FillCursor& c) {
+        if (++c.u == n_use) {
+            c.u = 0;
+            if (++c.ver == 2) { c.ver = 0; c.pair += gridDim.x; skip_pairs(c); }
         }
-        return;
+    };
+    auto issue_fill = [&](const FillCursor& c, uint32_t slot) {      // one lane
+        const int64_t pv = c.pair * 2 + c.ver;
+        const char* src;
+        uint32_t bytes;
+        if (c.u < n_sc) {
+            const int k0 = c.u * kRowsPerSlot;
+            src = reinterpret_cast<const char*>(a.scalars) + ((size_t)pv * K + k0) * row_bytes;
+            bytes = (uint32_t)(min(kRowsPerSlot, K - k0) * row_bytes);
+        } else if (c.u == n_sc) {
+            src = reinterpret_cast<const char*>(a.buckets) + ((size_t)pv * B + (B - 1)) * row_bytes;
+            bytes = (uint32_t)row_bytes;
+        } else {
+            const int b0 = (c.u - n_sc - 1) * kRowsPerSlot;
+            src = reinterpret_cast<const char*>(a.buckets) + ((size_t)pv * B + b0) * row_bytes;
+            bytes = (uint32_t)(min(kRowsPerSlot, B - 1 - b0) * row_bytes);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // reads of the slot before the async write
+        mbar_arrive_expect_tx(full_bar + slot, bytes);
+        bulk_g2s(ring + (size_t)slot * a.slot_bytes, src, bytes, full_bar + slot);
+    };
+    FillCursor fill;
+    fill.pair = blockIdx.x; fill.ver = 0; fill.u = 0;
+    skip_pairs(fill);
+    for (int s = 0; s < a.n_slots; ++s) {          // prologue: fill the whole ring
+        if (tid == 0 && cursor_valid(fill)) issue_fill(fill, (uint32_t)s);
+        cursor_next(fill);
     }
 
     // ===== consumers =====
@@ -374,7 +375,6 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
     int* rec_i = reinterpret_cast<int*>(reinterpret_cast<double*>(smem + a.off_rec) + (size_t)R::kInts * n_cons) + tid;
 #define CG_REC(f) rec[(f) * n_cons]
 #define CG_RECI(f) rec_i[(f) * n_cons]        // ints: [0, kG*NQ) bstar, kG*NQ valid bytes, kG*NQ+1 stash valid bytes
-    const int n_sc = (K + kRowsPerSlot - 1) / kRowsPerSlot;
     const int pitch = p.row_pitch;
     uint32_t it = 0;
     int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
@@ -393,11 +393,19 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         return reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
     };
     auto release = [&]() {
+        const uint32_t slot = it % (uint32_t)a.n_slots;
         __syncwarp();
 #ifdef CG_TIMING
         CG_TADD(1, clock64() - t_acq);
 #endif
-        if (lane == 0) mbar_arrive(empty_bar + (it % (uint32_t)a.n_slots));
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(s_arr + slot, 1u) == (unsigned)a.consumer_warps - 1u) {   // last warp out refills
+                s_arr[slot] = 0u;
+                if (cursor_valid(fill)) issue_fill(fill, slot);
+            }
+        }
+        cursor_next(fill);
         ++it;
     };
     CG_T(tk0);
