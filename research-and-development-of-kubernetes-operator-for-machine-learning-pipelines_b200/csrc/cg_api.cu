@@ -251,7 +251,7 @@ __global__ void replay_kernel(const uint32_t* __restrict__ gate_bits, const uint
         const uint32_t* bits = gate_bits + i * n_words;
         const bool hp = has_previous ? has_previous[i] != 0 : true;
         const int st = start_tick ? start_tick[i] : p.start_tick;
-        decisions[i] = cg::replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, hp, st, p);
+        decisions[i] = cg::replay_schedule_bits(bits, n_words, hp, st, p);
     }
 }
 

@@ -200,8 +200,7 @@ __global__ void __launch_bounds__(512) general_kernel(const __grid_constant__ Ge
         if (tid == 0 && a.decisions) {
             const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
             const int st = a.start_tick ? a.start_tick[pair] : p.start_tick;
-            a.decisions[pair] = replay_schedule(
-                [&](int t) { return (s_bits[t >> 5] >> (t & 31)) & 1u; }, hp, st, p);
+            a.decisions[pair] = replay_schedule_bits(s_bits, n_words, hp, st, p);
         }
         __syncthreads();       // s_bits / stash free for the next pair
     }

@@ -192,4 +192,45 @@ CG_DEVINL cg_decision replay_schedule(BitFn gate_bit, bool has_previous, int sta
     return d;
 }
 
+// The same loop over a packed bit-vector (bit j%32 of word j/32 = promote at tick j).  When
+// retries are one tick apart (attempt_delay = tick step, the reference's 10 s / 10 s) a whole
+// inner `while attempt < max_attempts` loop (:300-345) collapses to one find-first-set over the
+// next max_attempts bits, so a canary costs ~9 short steps instead of up to 90 dependent reads.
+CG_DEVINL cg_decision replay_schedule_bits(const uint32_t* bits, int n_words, bool has_previous,
+                                           int start_tick, const cg_params& p) {
+    if (!has_previous || p.attempt_delay_ticks != 1 || p.max_attempts > 32 || start_tick < 0)
+        return replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, has_previous,
+                               start_tick, p);
+    int cur = p.init_current, prev = p.max_traffic - p.init_current;   // :186-187
+    int tick = start_tick, n_prom = 0, n_eval = 0, last = -1;
+    int state = CG_STATE_IN_PROGRESS;
+    while (cur < p.max_traffic) {                                      // :296
+        const int avail = p.n_ticks - tick;
+        if (avail <= 0) break;                                         // ran out of data
+        const int n_try = avail < p.max_attempts ? avail : p.max_attempts;
+        const int w = tick >> 5;
+        const uint32_t lo = bits[w], hi = (w + 1 < n_words) ? bits[w + 1] : 0u;
+        uint32_t win = __funnelshift_r(lo, hi, tick & 31);
+        if (n_try < 32) win &= (1u << n_try) - 1u;
+        if (win) {                                                     // :310 succeeds at attempt k
+            const int k = __ffs(win) - 1;
+            n_eval += k + 1; last = tick + k;
+            cur += p.step; prev -= p.step;                             // :312-313
+            if (cur > p.max_traffic) cur = p.max_traffic;              // :316
+            if (prev < 0) prev = 0;                                    // :317
+            ++n_prom;
+            tick += k + p.interval_ticks;                              // :352
+        } else {
+            n_eval += n_try; last = tick + n_try - 1;
+            if (n_try == p.max_attempts) state = CG_STATE_ABORTED;     // :341-349
+            break;                                                     // else: data ended mid-retry
+        }
+    }
+    if (cur == p.max_traffic) state = CG_STATE_COMPLETE;               // :355
+    cg_decision d;
+    d.traffic_current = cur; d.traffic_prev = prev; d.state = state;
+    d.n_promotions = n_prom; d.n_evals = n_eval; d.last_tick = last;
+    return d;
+}
+
 }  // namespace cg

@@ -153,7 +153,70 @@ __device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int
             else if (!top_inf || B < 2) m[j] = NAN;
             else { found[j] = false; scan = true; }
         }
-        if (scan) {
+        if (scan && B <= 64) {
+            // one pass: lane l holds buckets l and l+32; both windows are loaded before any
+            // arithmetic so the global loads overlap
+            double v0 = -INFINITY, v1 = -INFINITY;
+            {
+                double x0[8], x1[8];
+                const bool h0 = lane < B, h1 = lane + 32 < B, small = g.n <= 8;
+                const T* r0 = bk + (size_t)lane * p.row_pitch + g.i0;
+                const T* r1 = bk + (size_t)(lane + 32) * p.row_pitch + g.i0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    x0[i] = (small && h0 && i < g.n) ? (double)r0[i] : 0.0;
+                    x1[i] = (small && h1 && i < g.n) ? (double)r1[i] : 0.0;
+                }
+                if (small) {
+                    double res0 = 0.0, res1 = 0.0;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {     // last - first (+ value before each reset, in order)
+                        if (i == g.n - 1) { res0 = x0[i] - x0[0]; res1 = x1[i] - x1[0]; }
+                    }
+#pragma unroll
+                    for (int i = 1; i < 8; ++i)
+                        if (i < g.n) {
+                            if (x0[i] < x0[i - 1]) res0 += x0[i - 1];
+                            if (x1[i] < x1[i - 1]) res1 += x1[i - 1];
+                        }
+                    if (h0) v0 = extrapolate(res0, x0[0], g) / range_s;
+                    if (h1) v1 = extrapolate(res1, x1[0], g) / range_s;
+                } else {
+                    if (h0) v0 = series_increase(bk + (size_t)lane * p.row_pitch, g) / range_s;
+                    if (h1) v1 = series_increase(bk + (size_t)(lane + 32) * p.row_pitch, g) / range_s;
+                }
+            }
+            for (int d = 1; d < 32; d <<= 1) {        // running max in bucket order (monotonic fix)
+                const double o0 = __shfl_up_sync(kFull, v0, d), o1 = __shfl_up_sync(kFull, v1, d);
+                if (lane >= d && o0 > v0) v0 = o0;
+                if (lane >= d && o1 > v1) v1 = o1;
+            }
+            const double carry = __shfl_sync(kFull, v0, 31);
+            if (B > 32 && carry > v1) v1 = carry;
+            const double obs = B <= 32 ? __shfl_sync(kFull, v0, B - 1) : __shfl_sync(kFull, v1, B - 33);
+            if (obs == 0) {
+                for (int j = 0; j < nq; ++j) if (!found[j]) { m[j] = NAN; found[j] = true; }
+            } else {
+                for (int j = 0; j < nq; ++j) {
+                    if (found[j]) continue;
+                    const double rank = p.q[j] * obs;
+                    const unsigned hit0 = __ballot_sync(kFull, lane < B - 1 && v0 >= rank);
+                    const unsigned hit1 = __ballot_sync(kFull, lane + 32 < B - 1 && v1 >= rank);
+                    if (!hit0 && !hit1) { m[j] = s_le[B - 2]; continue; }
+                    const int src = hit0 ? __ffs(hit0) - 1 : __ffs(hit1) - 1;
+                    const int bb = hit0 ? src : src + 32;
+                    const double cbv = __shfl_sync(kFull, hit0 ? v0 : v1, src);
+                    const double up = __shfl_sync(kFull, hit0 ? v0 : v1, src > 0 ? src - 1 : 0);
+                    const double cpv = src > 0 ? up : carry;     // (bb == 32: the last bucket of the lower half)
+                    if (bb == 0 && s_le[0] <= 0) m[j] = s_le[0];
+                    else {
+                        double start = 0.0, end = s_le[bb], cc = cbv, rk = rank;
+                        if (bb > 0) { start = s_le[bb - 1]; cc -= cpv; rk -= cpv; }
+                        m[j] = start + (end - start) * (rk / cc);
+                    }
+                }
+            }
+        } else if (scan) {
             const int chunks = (B + 31) >> 5;
             // pass 1: observations = last count after the running-max fix
             double carry = -INFINITY, obs = 0.0;
@@ -265,13 +328,15 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
     }
     const double res[kG] = {w0, O1 == 0 ? w0 : w1, O2 == 1 ? w1 : w2};
     const double fst[kG] = {x[0], x[O1], x[O2]};
+    // One multiply proves that the zero-point clamp cannot fire (first_v * gchk >= result, with
+    // gchk a slight under-estimate of sampled/d_start); lanes that fail it take the exact path.
     bool slow[kG];
 #pragma unroll
     for (int s = 0; s < kG; ++s) {
         slow[s] = !(fst[s] * h.gchk[s] >= res[s]) && ((live >> s) & 1u);
         inc[s] = res[s] * h.f[s];
     }
-    if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   // rare: the zero-point clamp may fire
+    if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   // rare: a counter that restarted one scrape ago
 #pragma unroll
         for (int s = 0; s < kG; ++s)
             if (slow[s]) inc[s] = slow_increase(a, phase, tick0 + s, res[s], fst[s]);
@@ -559,28 +624,33 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     for (int k = 0; k < nr; ++k) {
                         double inc[kG];
                         row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, live, inc);
-                        double c[kG];
-                        bool any_hit = false;
+                        // common case: increases are monotone in the bucket index and below the
+                        // search threshold -> prev = inc.  One vote decides whether any lane needs
+                        // the monotonic fix (Appendix A step 3) or has reached its rank.
+                        bool rare = false;
 #pragma unroll
                         for (int s = 0; s < kG; ++s) {
-                            c[s] = inc[s] < h.prev[s] ? h.prev[s] : inc[s];   // monotonic fix (Appendix A step 3)
+                            rare |= inc[s] < h.prev[s];
 #pragma unroll
-                            for (int q = 0; q < NQ; ++q) any_hit |= c[s] >= h.x0[s][q];
+                            for (int q = 0; q < NQ; ++q) rare |= inc[s] >= h.x0[s][q];
                         }
-                        if (__any_sync(kFull, any_hit)) {       // some lane's first bucket reaching the rank
+                        if (__any_sync(kFull, rare)) {
 #pragma unroll
-                            for (int s = 0; s < kG; ++s)
+                            for (int s = 0; s < kG; ++s) {
+                                const double c = inc[s] < h.prev[s] ? h.prev[s] : inc[s];
 #pragma unroll
                                 for (int q = 0; q < NQ; ++q)
-                                    if (c[s] >= h.x0[s][q]) {
+                                    if (c >= h.x0[s][q]) {      // first bucket reaching the rank
                                         CG_RECI(s * NQ + q) = b0 + k;
-                                        CG_REC(R::kCb + s * NQ + q) = c[s];
+                                        CG_REC(R::kCb + s * NQ + q) = c;
                                         CG_REC(R::kCprev + s * NQ + q) = h.prev[s];
                                         h.x0[s][q] = NAN;       // never true again
                                     }
+                                inc[s] = c;
+                            }
                         }
 #pragma unroll
-                        for (int s = 0; s < kG; ++s) h.prev[s] = c[s];
+                        for (int s = 0; s < kG; ++s) h.prev[s] = inc[s];
                     }
                     release();
                 }
@@ -588,8 +658,12 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             if (p.reserved & 2) continue;   // (reserved bit 1: debugging aid, skip the per-tick finish)
             CG_T(tf0);
             // ---- finish each tick: histogram_quantile (Appendix A) from the captured search state
-            if (B > 0 && active) {
+            if (B > 0 && active && !(p.reserved & 8)) {
+                // Straight-line per (tick, quantile): every candidate value is computed, then one
+                // chain of selects picks the case, so the three ticks overlap in the pipelines.
                 const bool top_inf = isinf(s_le[B - 1]) && s_le[B - 1] > 0;
+                const bool shape_ok = top_inf && B >= 2;
+                const double le_lo = s_le[0], le_top = B >= 2 ? s_le[B - 2] : NAN;
 #pragma unroll
                 for (int s = 0; s < kG; ++s) {
                     if (s >= n_mine) continue;
@@ -597,30 +671,29 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     // observations after the monotonic fix; the search assumed the +Inf bucket itself
                     const bool spec_ok = !(obs_inc < h.prev[s]);
                     const double obs = div_const(obs_inc, a.range_s, a.rc_range);
-                    for (int q = 0; q < p.n_q; ++q) {
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q) {
+                        if (q >= p.n_q) continue;
                         const double qq = p.q[q];
-                        double r;
-                        if (isnan(qq)) r = NAN;
-                        else if (qq < 0) r = -INFINITY;
-                        else if (qq > 1) r = INFINITY;
-                        else if (!top_inf || B < 2) r = NAN;
-                        else if (!spec_ok) { fb_mask |= 1u << s; r = NAN; }
-                        else if (obs == 0) r = NAN;
-                        else if (CG_RECI(s * NQ + q) < 0) r = s_le[B - 2];
-                        else {
-                            const int bb = CG_RECI(s * NQ + q);
-                            const double rank = qq * obs;
-                            const double cbr = div_const(CG_REC(R::kCb + s * NQ + q), a.range_s, a.rc_range);
-                            const double cpr = bb > 0 ? div_const(CG_REC(R::kCprev + s * NQ + q), a.range_s, a.rc_range) : 0.0;
-                            // the search ran in increase space; confirm it in rate space
-                            if (!(cbr >= rank) || (bb > 0 && !(cpr < rank))) { fb_mask |= 1u << s; r = NAN; }
-                            else if (bb == 0 && s_le[0] <= 0) r = s_le[0];
-                            else {
-                                double start = 0.0, end = s_le[bb], cc = cbr, rk = rank;
-                                if (bb > 0) { start = s_le[bb - 1]; cc -= cpr; rk -= cpr; }
-                                r = start + (end - start) * (rk / cc);
-                            }
-                        }
+                        const int bb = CG_RECI(s * NQ + q);
+                        const int bi = bb > 0 ? bb : 0;
+                        const double rank = qq * obs;
+                        const double cbr = div_const(CG_REC(R::kCb + s * NQ + q), a.range_s, a.rc_range);
+                        const double cpr = div_const(CG_REC(R::kCprev + s * NQ + q), a.range_s, a.rc_range);
+                        const double start = bb > 0 ? s_le[bi - 1] : 0.0, end = s_le[bi];
+                        const double cc = bb > 0 ? cbr - cpr : cbr, rk = bb > 0 ? rank - cpr : rank;
+                        const double interp = start + (end - start) * (rk / cc);
+                        // the search ran in increase space; confirm it in rate space
+                        const bool confirmed = (cbr >= rank) && (bb <= 0 || cpr < rank);
+                        const bool q_ok = !isnan(qq) && qq >= 0 && qq <= 1;
+                        const bool searched = q_ok && shape_ok && obs != 0;
+                        double r = interp;
+                        if (bb == 0 && le_lo <= 0) r = le_lo;
+                        if (bb < 0) r = le_top;
+                        if (!searched) r = NAN;                       // bad shape, q is NaN, or no observations
+                        if (qq < 0) r = -INFINITY;
+                        if (qq > 1) r = INFINITY;
+                        if (searched && (!spec_ok || (bb >= 0 && !confirmed))) fb_mask |= 1u << s;
                         if (q == p.gate_q) CG_REC(R::kQv + s) = r;
                         if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick0 + s) * W + q] = r;
                     }
@@ -634,7 +707,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             // ---- exact re-evaluation of whatever the fast path could not decide
 #pragma unroll 1
             for (int s = 0; s < kG; ++s) {
-                unsigned todo = __ballot_sync(kFull, (fb_mask >> s) & 1u);
+                unsigned todo = __ballot_sync(kFull, ((fb_mask >> s) & 1u) && !(p.reserved & 4));
                 while (todo) {
                     CG_TADD(7, 1);
                     const int src = __ffs(todo) - 1;
@@ -659,6 +732,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             CG_T(tq2);
             CG_TADD(9, tq2 - tq1);
             // ---- the new version's gate inputs wait for the old version's pass; then the gate
+            if (p.reserved & 16) continue;
             if (ver == 0) {
 #pragma unroll
                 for (int s = 0; s < kG; ++s) {
@@ -696,7 +770,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             if (a.gate_bits) for (int w = lane; w < n_words; w += 32) a.gate_bits[pair * n_words + w] = bits[w];
             if (lane == 0) {
                 const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
-                a.decisions[pair] = replay_schedule([&](int t) { return (bits[t >> 5] >> (t & 31)) & 1u; }, true, st_tick, p);
+                a.decisions[pair] = replay_schedule_bits(bits, n_words, true, st_tick, p);
             }
         }
         bit_buf = (bit_buf + 1) % 3;
