@@ -140,6 +140,7 @@ bool stream_eligible(const cg_params* p) {
     if ((int64_t)p->window_ms != 4 * (int64_t)p->period_ms) return false;
     if (3 * (int64_t)p->tick_step_ms != 2 * (int64_t)p->period_ms) return false;
     if (p->n_scalar + p->n_buckets == 0 || p->n_ticks < 1) return false;
+    if (p->n_buckets > 64 || p->n_scalar < 1) return false;   // exact fallback holds two buckets per lane; ratios come from the scalar rows
     if (p->n_samples < 4) return false;
     const int groups = (p->n_ticks + cg::kG - 1) / cg::kG;
     if (groups > 15 * 32) return false;

@@ -61,12 +61,16 @@ CG_DEVINL TickGeom tick_geom(const cg_params& p, int32_t phase, int tick) {
 // against true division on 2e8 random doubles over 80 binades and every integer in [-3e5, 4e6]
 // for each constant used here (tests/test_div_const.py keeps a smaller version of that check).
 // Magnitudes near the overflow / underflow ends take the true division.
+// Out-of-line IEEE division: one copy of the ~40-instruction sequence instead of one per use in
+// code that runs once per (pair, version) and has to stay small for the instruction cache.
+static __device__ __noinline__ double ddiv_call(double a, double b) { return a / b; }
+
 CG_DEVINL double div_const(double a, double c, double rc) {
     const double q = a * rc;
     const double r = fma(-q, c, a);
     const double q2 = fma(r, rc, q);
     const double aa = fabs(a);
-    if (!(aa < 1e300 && (aa > 1e-290 || a == 0.0))) return a / c;
+    if (!(aa < 1e300 && (aa > 1e-290 || a == 0.0))) return ddiv_call(a, c);
     return q2;
 }
 

@@ -111,13 +111,17 @@ struct Rec {                       // field indices of the shared-memory record 
     static constexpr int kDoubles = kInts + (kG * NQ + 2 + 1) / 2;
 };
 
+static __device__ __noinline__ double extrapolate_call(double result, double first_v, const TickGeom& g) {
+    return extrapolate(result, first_v, g);
+}
+
 // ---- warp-cooperative exact evaluation of one (pair, version, tick) from global memory
 template <typename T>
 __device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int32_t phase, int tick, int lane,
                                const double* __restrict__ s_le, double* m, uint8_t& valid_out) {
     const cg_params& p = a.p;
     const int nq = p.n_q, K = p.n_scalar, B = p.n_buckets;
-    const TickGeom g = tick_geom(p, phase, tick);
+    const TickGeom g = tick_geom32(p, phase, tick);   // the eligibility test bounds every time stamp
     const T* sc = reinterpret_cast<const T*>(a.scalars) + (size_t)pv * K * p.row_pitch;
     const T* bk = reinterpret_cast<const T*>(a.buckets) + (size_t)pv * B * p.row_pitch;
     uint8_t valid = 0;
@@ -153,38 +157,32 @@ __device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int
             else if (!top_inf || B < 2) m[j] = NAN;
             else { found[j] = false; scan = true; }
         }
-        if (scan && B <= 64) {
+        if (scan) {   // B <= 64 (eligibility test of the streaming kernel)
             // one pass: lane l holds buckets l and l+32; both windows are loaded before any
             // arithmetic so the global loads overlap
             double v0 = -INFINITY, v1 = -INFINITY;
             {
                 double x0[8], x1[8];
-                const bool h0 = lane < B, h1 = lane + 32 < B, small = g.n <= 8;
+                const bool h0 = lane < B, h1 = lane + 32 < B;   // g.n <= 5: the window is 4 scrape periods
                 const T* r0 = bk + (size_t)lane * p.row_pitch + g.i0;
                 const T* r1 = bk + (size_t)(lane + 32) * p.row_pitch + g.i0;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    x0[i] = (small && h0 && i < g.n) ? (double)r0[i] : 0.0;
-                    x1[i] = (small && h1 && i < g.n) ? (double)r1[i] : 0.0;
+                    x0[i] = (h0 && i < g.n) ? (double)r0[i] : 0.0;
+                    x1[i] = (h1 && i < g.n) ? (double)r1[i] : 0.0;
                 }
-                if (small) {
-                    double res0 = 0.0, res1 = 0.0;
+                double res0 = 0.0, res1 = 0.0;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {     // last - first (+ value before each reset, in order)
-                        if (i == g.n - 1) { res0 = x0[i] - x0[0]; res1 = x1[i] - x1[0]; }
+                for (int i = 0; i < 8; ++i)           // last - first (+ value before each reset, in order)
+                    if (i == g.n - 1) { res0 = x0[i] - x0[0]; res1 = x1[i] - x1[0]; }
+#pragma unroll
+                for (int i = 1; i < 8; ++i)
+                    if (i < g.n) {
+                        if (x0[i] < x0[i - 1]) res0 += x0[i - 1];
+                        if (x1[i] < x1[i - 1]) res1 += x1[i - 1];
                     }
-#pragma unroll
-                    for (int i = 1; i < 8; ++i)
-                        if (i < g.n) {
-                            if (x0[i] < x0[i - 1]) res0 += x0[i - 1];
-                            if (x1[i] < x1[i - 1]) res1 += x1[i - 1];
-                        }
-                    if (h0) v0 = extrapolate(res0, x0[0], g) / range_s;
-                    if (h1) v1 = extrapolate(res1, x1[0], g) / range_s;
-                } else {
-                    if (h0) v0 = series_increase(bk + (size_t)lane * p.row_pitch, g) / range_s;
-                    if (h1) v1 = series_increase(bk + (size_t)(lane + 32) * p.row_pitch, g) / range_s;
-                }
+                if (h0) v0 = ddiv_call(extrapolate_call(res0, x0[0], g), range_s);
+                if (h1) v1 = ddiv_call(extrapolate_call(res1, x1[0], g), range_s);
             }
             for (int d = 1; d < 32; d <<= 1) {        // running max in bucket order (monotonic fix)
                 const double o0 = __shfl_up_sync(kFull, v0, d), o1 = __shfl_up_sync(kFull, v1, d);
@@ -212,72 +210,17 @@ __device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int
                     else {
                         double start = 0.0, end = s_le[bb], cc = cbv, rk = rank;
                         if (bb > 0) { start = s_le[bb - 1]; cc -= cpv; rk -= cpv; }
-                        m[j] = start + (end - start) * (rk / cc);
+                        m[j] = start + (end - start) * ddiv_call(rk, cc);
                     }
                 }
-            }
-        } else if (scan) {
-            const int chunks = (B + 31) >> 5;
-            // pass 1: observations = last count after the running-max fix
-            double carry = -INFINITY, obs = 0.0;
-            for (int c = 0; c < chunks; ++c) {
-                const int b = (c << 5) + lane;
-                double v = -INFINITY;
-                if (b < B) v = series_increase(bk + (size_t)b * p.row_pitch, g) / range_s;
-                for (int d = 1; d < 32; d <<= 1) {
-                    const double o = __shfl_up_sync(kFull, v, d);
-                    if (lane >= d && o > v) v = o;
-                }
-                if (carry > v) v = carry;
-                const int last = min(31, B - 1 - (c << 5));
-                carry = __shfl_sync(kFull, v, last);
-                obs = carry;
-            }
-            if (obs == 0) {
-                for (int j = 0; j < nq; ++j) if (!found[j]) { m[j] = NAN; found[j] = true; }
-            } else {
-                double rank[CG_MAX_Q];
-                for (int j = 0; j < nq; ++j) rank[j] = p.q[j] * obs;
-                carry = -INFINITY;
-                for (int c = 0; c < chunks; ++c) {
-                    const int b = (c << 5) + lane;
-                    double v = -INFINITY;
-                    if (b < B) v = series_increase(bk + (size_t)b * p.row_pitch, g) / range_s;
-                    for (int d = 1; d < 32; d <<= 1) {
-                        const double o = __shfl_up_sync(kFull, v, d);
-                        if (lane >= d && o > v) v = o;
-                    }
-                    if (carry > v) v = carry;
-                    for (int j = 0; j < nq; ++j) {
-                        if (found[j]) continue;
-                        const unsigned hit = __ballot_sync(kFull, b < B - 1 && v >= rank[j]);
-                        if (hit) {
-                            const int src = __ffs(hit) - 1;
-                            const int bb = (c << 5) + src;
-                            const double cbv = __shfl_sync(kFull, v, src);
-                            const double up = __shfl_sync(kFull, v, src > 0 ? src - 1 : 0);
-                            const double cpv = src > 0 ? up : carry;
-                            found[j] = true;
-                            if (bb == 0 && s_le[0] <= 0) m[j] = s_le[0];
-                            else {
-                                double start = 0.0, end = s_le[bb], cc = cbv, rk = rank[j];
-                                if (bb > 0) { start = s_le[bb - 1]; cc -= cpv; rk -= cpv; }
-                                m[j] = start + (end - start) * (rk / cc);
-                            }
-                        }
-                    }
-                    const int last = min(31, B - 1 - (c << 5));
-                    carry = __shfl_sync(kFull, v, last);
-                }
-                for (int j = 0; j < nq; ++j) if (!found[j]) m[j] = s_le[B - 2];
             }
         }
     }
     const double total = sums[0], err = sums[1], lat_sum = sums[2], lat_cnt = sums[3], fb = sums[4];
     m[nq + CG_M_ERROR_RESPONSES] = err;
-    if (total > 0) { m[nq + CG_M_ERROR_RATE] = err / total; valid |= CG_V_ERROR_RATE; }
+    if (total > 0) { m[nq + CG_M_ERROR_RATE] = ddiv_call(err, total); valid |= CG_V_ERROR_RATE; }
     else m[nq + CG_M_ERROR_RATE] = NAN;
-    if (lat_cnt > 0) { m[nq + CG_M_LATENCY_AVG] = lat_sum / lat_cnt; valid |= CG_V_LATENCY_AVG; }
+    if (lat_cnt > 0) { m[nq + CG_M_LATENCY_AVG] = ddiv_call(lat_sum, lat_cnt); valid |= CG_V_LATENCY_AVG; }
     else m[nq + CG_M_LATENCY_AVG] = NAN;
     m[nq + CG_M_REQUEST_COUNT] = lat_cnt;
     m[nq + CG_M_FEEDBACK_COUNT] = fb;
@@ -305,29 +248,30 @@ static __device__ __noinline__ double slow_increase(const StreamArgs& a, int32_t
     return extrapolate(result, first_v, g);
 }
 
-// Window deltas and fast increases of one row for the thread's kG ticks.  O1 / O2: tile offsets of
-// the windows of tick 1 and tick 2 (tick 0 is at offset 0); the patterns that occur are (0,1),
-// (1,1), (1,2) and depend only on the series phase.  All 32 lanes call this.
-template <typename T, int NQ, int O1, int O2>
+// Window deltas and fast increases of one row for the thread's kG ticks.  o1 / o2 (warp-uniform):
+// tick 1 uses the window at tile offset (o1 ? 1 : 0), tick 2 the one at (o2 ? 2 : 1); tick 0 is at
+// offset 0.  The pattern depends only on the series phase.  One copy of this code serves every
+// pattern and every kind of row: the kernel's hot loop has to stay small for the instruction cache.
+// All 32 lanes call this.
+template <typename T, int NQ>
 __device__ __forceinline__ void row_increases(const T* __restrict__ row, const Hot<NQ>& h, const StreamArgs& a,
                                               const int32_t phase, const int tick0, const unsigned live,
-                                              double (&inc)[kG]) {
+                                              const bool o1, const bool o2, double (&inc)[kG]) {
     double x[6];
     Tile6<T>::load(row, x);
-    double w0 = x[3] - x[0], w1 = x[4] - x[1], w2 = (O2 == 2) ? x[5] - x[2] : 0.0;
-    const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3],
-               r5 = (O2 == 2) && x[5] < x[4];
+    double w0 = x[3] - x[0], w1 = x[4] - x[1], w2 = x[5] - x[2];
+    const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3], r5 = o2 && x[5] < x[4];
     // `live`: bit s set when tick s of this thread is evaluated by the fast path; lanes and tick
     // slots that are not (idle lanes, a partial last group) must never drag the warp into a rare path
     if (__any_sync(kFull, (r1 | r2 | r3 | r4 | r5) && live)) {   // counter resets are rare (Appendix A step 2)
         if (r1) w0 += x[0];
         if (r2) { w0 += x[1]; w1 += x[1]; }
-        if (r3) { w0 += x[2]; w1 += x[2]; if (O2 == 2) w2 += x[2]; }
-        if (r4) { w1 += x[3]; if (O2 == 2) w2 += x[3]; }
+        if (r3) { w0 += x[2]; w1 += x[2]; w2 += x[2]; }
+        if (r4) { w1 += x[3]; w2 += x[3]; }
         if (r5) w2 += x[4];
     }
-    const double res[kG] = {w0, O1 == 0 ? w0 : w1, O2 == 1 ? w1 : w2};
-    const double fst[kG] = {x[0], x[O1], x[O2]};
+    const double res[kG] = {w0, o1 ? w1 : w0, o2 ? w2 : w1};
+    const double fst[kG] = {x[0], o1 ? x[1] : x[0], o2 ? x[2] : x[1]};
     // One multiply proves that the zero-point clamp cannot fire (first_v * gchk >= result, with
     // gchk a slight under-estimate of sampled/d_start); lanes that fail it take the exact path.
     bool slow[kG];
@@ -341,15 +285,6 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
         for (int s = 0; s < kG; ++s)
             if (slow[s]) inc[s] = slow_increase(a, phase, tick0 + s, res[s], fst[s]);
     }
-}
-
-template <typename T, int NQ>
-__device__ __forceinline__ void row_increases_pat(const int pat, const T* __restrict__ row, const Hot<NQ>& h,
-                                                  const StreamArgs& a, const int32_t phase, const int tick0,
-                                                  const unsigned live, double (&inc)[kG]) {
-    if (pat == 0) row_increases<T, NQ, 0, 1>(row, h, a, phase, tick0, live, inc);
-    else if (pat == 1) row_increases<T, NQ, 1, 1>(row, h, a, phase, tick0, live, inc);
-    else row_increases<T, NQ, 1, 2>(row, h, a, phase, tick0, live, inc);
 }
 
 // Position in a CTA's stream of ring fills: (pair, version, slot-use within the version).
@@ -552,78 +487,28 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             for (int q = 0; q < kG * NQ; ++q) CG_RECI(q) = -1;
 
             CG_TADD(2, clock64() - ts0);
-            // ---- scalar counter rows: sum(increase(...)) per role, in series order (:375-410)
-            {
-                double sums[kG][5];
-                unsigned have = 0;
+            // ---- the row stream: K scalar rows (sum(increase(...)) per role, :375-410), the +Inf
+            // bucket (observations -> rank -> search threshold), then bucket rows 0..B-2 (monotonic
+            // fix and the search for the rank, in bucket order).  One loop, one copy of the row code.
+            const bool o1 = pat != 0, o2 = pat == 2;
+            double sums[kG][5];
+            unsigned have = 0;
 #pragma unroll
-                for (int s = 0; s < kG; ++s)
+            for (int s = 0; s < kG; ++s)
 #pragma unroll
-                    for (int q = 0; q < 5; ++q) sums[s][q] = 0.0;
-                for (int u = 0; u < n_sc; ++u) {
-                    const T* rows = acquire();
-                    const int k0 = u * kRowsPerSlot, nr = min(kRowsPerSlot, K - k0);
-                    if (!(p.reserved & 1))
+                for (int q = 0; q < 5; ++q) sums[s][q] = 0.0;
 #pragma unroll 1
-                    for (int k = 0; k < nr; ++k) {
-                        double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, live, inc);
-                        const unsigned role = p.scalar_role[k0 + k];
-#pragma unroll
-                        for (int q = 0; q < 5; ++q)
-                            if (role & (1u << q)) {
-#pragma unroll
-                                for (int s = 0; s < kG; ++s) sums[s][q] = (have & (1u << q)) ? sums[s][q] + inc[s] : inc[s];
-                                have |= 1u << q;
-                            }
-                    }
-                    release();
-                }
-                // derived metrics (:387-404), validity, optional record output
-                unsigned vbytes = 0;
-#pragma unroll
-                for (int s = 0; s < kG; ++s) {
-                    const double total = sums[s][0], err = sums[s][1], lsum = sums[s][2], lcnt = sums[s][3];
-                    unsigned valid = (B > 0) ? CG_V_QUANTILE : 0u;
-                    double er = NAN, avg = NAN;
-                    if (total > 0) { er = err / total; valid |= CG_V_ERROR_RATE; }
-                    if (lcnt > 0) { avg = lsum / lcnt; valid |= CG_V_LATENCY_AVG; }
-                    CG_REC(R::kEr + s) = er;
-                    CG_REC(R::kAvg + s) = avg;
-                    vbytes |= valid << (8 * s);
-                    if (a.metrics && s < n_mine && active) {
-                        double* o = a.metrics + ((size_t)pv * p.n_ticks + tick0 + s) * W + p.n_q;
-                        o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
-                        o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[s][4];
-                    }
-                }
-                CG_RECI(kG * NQ) = (int)vbytes;
-            }
-            if (B > 0) {
-                {   // ---- the +Inf bucket first: observations -> rank -> search threshold
-                    const T* rows = acquire();
-                    if (!(p.reserved & 1)) {
-                        double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + base, h, a, phase, tick0, live, inc);
-#pragma unroll
-                        for (int s = 0; s < kG; ++s) {
-                            CG_REC(R::kObs + s) = inc[s];
-                            const double obs = div_const(inc[s], a.range_s, a.rc_range);
-#pragma unroll
-                            for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * a.range_s : NAN;
-                        }
-                    }
-                    release();
-                }
-                // ---- bucket rows 0..B-2: monotonic fix and the search for the rank, in bucket order
-                for (int b0 = 0; b0 < B - 1; b0 += kRowsPerSlot) {
-                    const T* rows = acquire();
-                    const int nr = min(kRowsPerSlot, B - 1 - b0);
-                    if (!(p.reserved & 1))
+            for (int u = 0; u < n_use; ++u) {
+                const T* rows = acquire();
+                const int kind = u < n_sc ? 0 : (u == n_sc ? 1 : 2);
+                const int first = kind == 0 ? u * kRowsPerSlot : (kind == 1 ? B - 1 : (u - n_sc - 1) * kRowsPerSlot);
+                const int nr = kind == 0 ? min(kRowsPerSlot, K - first) : (kind == 1 ? 1 : min(kRowsPerSlot, B - 1 - first));
+                if (!(p.reserved & 1))
 #pragma unroll 1
-                    for (int k = 0; k < nr; ++k) {
-                        double inc[kG];
-                        row_increases_pat<T, NQ>(pat, rows + k * pitch + base, h, a, phase, tick0, live, inc);
+                for (int k = 0; k < nr; ++k) {
+                    double inc[kG];
+                    row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, live, o1, o2, inc);
+                    if (kind == 2) {
                         // common case: increases are monotone in the bucket index and below the
                         // search threshold -> prev = inc.  One vote decides whether any lane needs
                         // the monotonic fix (Appendix A step 3) or has reached its rank.
@@ -641,7 +526,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll
                                 for (int q = 0; q < NQ; ++q)
                                     if (c >= h.x0[s][q]) {      // first bucket reaching the rank
-                                        CG_RECI(s * NQ + q) = b0 + k;
+                                        CG_RECI(s * NQ + q) = first + k;
                                         CG_REC(R::kCb + s * NQ + q) = c;
                                         CG_REC(R::kCprev + s * NQ + q) = h.prev[s];
                                         h.x0[s][q] = NAN;       // never true again
@@ -651,8 +536,46 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         }
 #pragma unroll
                         for (int s = 0; s < kG; ++s) h.prev[s] = inc[s];
+                    } else if (kind == 0) {
+                        const unsigned role = p.scalar_role[first + k];
+#pragma unroll
+                        for (int q = 0; q < 5; ++q)
+                            if (role & (1u << q)) {
+#pragma unroll
+                                for (int s = 0; s < kG; ++s) sums[s][q] = (have & (1u << q)) ? sums[s][q] + inc[s] : inc[s];
+                                have |= 1u << q;
+                            }
+                    } else {
+#pragma unroll
+                        for (int s = 0; s < kG; ++s) {
+                            CG_REC(R::kObs + s) = inc[s];
+                            const double obs = div_const(inc[s], a.range_s, a.rc_range);
+#pragma unroll
+                            for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * a.range_s : NAN;
+                        }
                     }
-                    release();
+                }
+                release();
+                if (u == n_sc - 1 || (n_sc == 0 && u == 0)) {
+                    // derived metrics (:387-404), validity, optional record output
+                    unsigned vbytes = 0;
+#pragma unroll
+                    for (int s = 0; s < kG; ++s) {
+                        const double total = sums[s][0], err = sums[s][1], lsum = sums[s][2], lcnt = sums[s][3];
+                        unsigned valid = (B > 0) ? CG_V_QUANTILE : 0u;
+                        double er = NAN, avg = NAN;
+                        if (total > 0) { er = ddiv_call(err, total); valid |= CG_V_ERROR_RATE; }
+                        if (lcnt > 0) { avg = ddiv_call(lsum, lcnt); valid |= CG_V_LATENCY_AVG; }
+                        CG_REC(R::kEr + s) = er;
+                        CG_REC(R::kAvg + s) = avg;
+                        vbytes |= valid << (8 * s);
+                        if (a.metrics && s < n_mine && active) {
+                            double* o = a.metrics + ((size_t)pv * p.n_ticks + tick0 + s) * W + p.n_q;
+                            o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
+                            o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[s][4];
+                        }
+                    }
+                    CG_RECI(kG * NQ) = (int)vbytes;
                 }
             }
             if (p.reserved & 2) continue;   // (reserved bit 1: debugging aid, skip the per-tick finish)
@@ -664,12 +587,14 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                 const bool top_inf = isinf(s_le[B - 1]) && s_le[B - 1] > 0;
                 const bool shape_ok = top_inf && B >= 2;
                 const double le_lo = s_le[0], le_top = B >= 2 ? s_le[B - 2] : NAN;
+                // observations after the monotonic fix; the search assumed the +Inf bucket itself
+                unsigned spec_bad = 0;
 #pragma unroll
-                for (int s = 0; s < kG; ++s) {
-                    if (s >= n_mine) continue;
+                for (int s = 0; s < kG; ++s) if (CG_REC(R::kObs + s) < h.prev[s]) spec_bad |= 1u << s;
+#pragma unroll 1
+                for (int s = 0; s < n_mine; ++s) {
                     const double obs_inc = CG_REC(R::kObs + s);
-                    // observations after the monotonic fix; the search assumed the +Inf bucket itself
-                    const bool spec_ok = !(obs_inc < h.prev[s]);
+                    const bool spec_ok = !((spec_bad >> s) & 1u);
                     const double obs = div_const(obs_inc, a.range_s, a.rc_range);
 #pragma unroll
                     for (int q = 0; q < NQ; ++q) {
@@ -682,7 +607,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         const double cpr = div_const(CG_REC(R::kCprev + s * NQ + q), a.range_s, a.rc_range);
                         const double start = bb > 0 ? s_le[bi - 1] : 0.0, end = s_le[bi];
                         const double cc = bb > 0 ? cbr - cpr : cbr, rk = bb > 0 ? rank - cpr : rank;
-                        const double interp = start + (end - start) * (rk / cc);
+                        const double interp = start + (end - start) * ddiv_call(rk, cc);
                         // the search ran in increase space; confirm it in rate space
                         const bool confirmed = (cbr >= rank) && (bb <= 0 || cpr < rank);
                         const bool q_ok = !isnan(qq) && qq >= 0 && qq <= 1;
@@ -743,9 +668,8 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                 CG_RECI(kG * NQ + 1) = CG_RECI(kG * NQ);
             } else {
                 const int nvb = CG_RECI(kG * NQ + 1), ovb = CG_RECI(kG * NQ);
-#pragma unroll
-                for (int s = 0; s < kG; ++s) {
-                    if (s >= n_mine) continue;
+#pragma unroll 1
+                for (int s = 0; s < n_mine; ++s) {
                     const int tk = tick0 + s;
                     const double nm[3] = {CG_REC(R::kStash + s * 3 + 0), CG_REC(R::kStash + s * 3 + 1), CG_REC(R::kStash + s * 3 + 2)};
                     const double om[3] = {(p.n_q > 0) ? CG_REC(R::kQv + s) : NAN, CG_REC(R::kEr + s), CG_REC(R::kAvg + s)};
