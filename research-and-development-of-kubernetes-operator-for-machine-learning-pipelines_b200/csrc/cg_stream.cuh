@@ -491,24 +491,67 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             // bucket (observations -> rank -> search threshold), then bucket rows 0..B-2 (monotonic
             // fix and the search for the rank, in bucket order).  One loop, one copy of the row code.
             const bool o1 = pat != 0, o2 = pat == 2;
-            double sums[kG][5];
-            unsigned have = 0;
+            {   // scalar rows; the role sums live in registers only inside this block
+                double sums[kG][5];
+                unsigned have = 0;
 #pragma unroll
-            for (int s = 0; s < kG; ++s)
+                for (int s = 0; s < kG; ++s)
 #pragma unroll
-                for (int q = 0; q < 5; ++q) sums[s][q] = 0.0;
+                    for (int q = 0; q < 5; ++q) sums[s][q] = 0.0;
 #pragma unroll 1
-            for (int u = 0; u < n_use; ++u) {
+                for (int u = 0; u < n_sc; ++u) {
+                    const T* rows = acquire();
+                    const int first = u * kRowsPerSlot, nr = min(kRowsPerSlot, K - first);
+                    if (!(p.reserved & 1))
+#pragma unroll 1
+                    for (int k = 0; k < nr; ++k) {
+                        double inc[kG];
+                        row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, live, o1, o2, inc);
+                        const unsigned role = p.scalar_role[first + k];
+#pragma unroll
+                        for (int q = 0; q < 5; ++q)
+                            if (role & (1u << q)) {
+#pragma unroll
+                                for (int s = 0; s < kG; ++s) sums[s][q] = (have & (1u << q)) ? sums[s][q] + inc[s] : inc[s];
+                                have |= 1u << q;
+                            }
+                    }
+                    release();
+                }
+                // derived metrics (:387-404), validity, optional record output
+                unsigned vbytes = 0;
+#pragma unroll
+                for (int s = 0; s < kG; ++s) {
+                    const double total = sums[s][0], err = sums[s][1], lsum = sums[s][2], lcnt = sums[s][3];
+                    unsigned valid = (B > 0) ? CG_V_QUANTILE : 0u;
+                    double er = NAN, avg = NAN;
+                    if (total > 0) { er = ddiv_call(err, total); valid |= CG_V_ERROR_RATE; }
+                    if (lcnt > 0) { avg = ddiv_call(lsum, lcnt); valid |= CG_V_LATENCY_AVG; }
+                    CG_REC(R::kEr + s) = er;
+                    CG_REC(R::kAvg + s) = avg;
+                    vbytes |= valid << (8 * s);
+                    if (a.metrics && s < n_mine && active) {
+                        double* o = a.metrics + ((size_t)pv * p.n_ticks + tick0 + s) * W + p.n_q;
+                        o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
+                        o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[s][4];
+                    }
+                }
+                CG_RECI(kG * NQ) = (int)vbytes;
+            }
+            // ---- the +Inf bucket (observations -> rank -> search threshold), then bucket rows
+            // 0..B-2 (monotonic fix and the search for the rank, in bucket order): one loop
+#pragma unroll 1
+            for (int u = n_sc; u < n_use; ++u) {
                 const T* rows = acquire();
-                const int kind = u < n_sc ? 0 : (u == n_sc ? 1 : 2);
-                const int first = kind == 0 ? u * kRowsPerSlot : (kind == 1 ? B - 1 : (u - n_sc - 1) * kRowsPerSlot);
-                const int nr = kind == 0 ? min(kRowsPerSlot, K - first) : (kind == 1 ? 1 : min(kRowsPerSlot, B - 1 - first));
+                const bool is_inf = u == n_sc;
+                const int first = is_inf ? B - 1 : (u - n_sc - 1) * kRowsPerSlot;
+                const int nr = is_inf ? 1 : min(kRowsPerSlot, B - 1 - first);
                 if (!(p.reserved & 1))
 #pragma unroll 1
                 for (int k = 0; k < nr; ++k) {
                     double inc[kG];
                     row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, live, o1, o2, inc);
-                    if (kind == 2) {
+                    if (!is_inf) {
                         // common case: increases are monotone in the bucket index and below the
                         // search threshold -> prev = inc.  One vote decides whether any lane needs
                         // the monotonic fix (Appendix A step 3) or has reached its rank.
@@ -536,15 +579,6 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         }
 #pragma unroll
                         for (int s = 0; s < kG; ++s) h.prev[s] = inc[s];
-                    } else if (kind == 0) {
-                        const unsigned role = p.scalar_role[first + k];
-#pragma unroll
-                        for (int q = 0; q < 5; ++q)
-                            if (role & (1u << q)) {
-#pragma unroll
-                                for (int s = 0; s < kG; ++s) sums[s][q] = (have & (1u << q)) ? sums[s][q] + inc[s] : inc[s];
-                                have |= 1u << q;
-                            }
                     } else {
 #pragma unroll
                         for (int s = 0; s < kG; ++s) {
@@ -556,27 +590,6 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     }
                 }
                 release();
-                if (u == n_sc - 1 || (n_sc == 0 && u == 0)) {
-                    // derived metrics (:387-404), validity, optional record output
-                    unsigned vbytes = 0;
-#pragma unroll
-                    for (int s = 0; s < kG; ++s) {
-                        const double total = sums[s][0], err = sums[s][1], lsum = sums[s][2], lcnt = sums[s][3];
-                        unsigned valid = (B > 0) ? CG_V_QUANTILE : 0u;
-                        double er = NAN, avg = NAN;
-                        if (total > 0) { er = ddiv_call(err, total); valid |= CG_V_ERROR_RATE; }
-                        if (lcnt > 0) { avg = ddiv_call(lsum, lcnt); valid |= CG_V_LATENCY_AVG; }
-                        CG_REC(R::kEr + s) = er;
-                        CG_REC(R::kAvg + s) = avg;
-                        vbytes |= valid << (8 * s);
-                        if (a.metrics && s < n_mine && active) {
-                            double* o = a.metrics + ((size_t)pv * p.n_ticks + tick0 + s) * W + p.n_q;
-                            o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
-                            o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[s][4];
-                        }
-                    }
-                    CG_RECI(kG * NQ) = (int)vbytes;
-                }
             }
             if (p.reserved & 2) continue;   // (reserved bit 1: debugging aid, skip the per-tick finish)
             CG_T(tf0);
