@@ -255,15 +255,14 @@ static __device__ __noinline__ double slow_increase(const StreamArgs& a, int32_t
 // All 32 lanes call this.
 template <typename T, int NQ>
 __device__ __forceinline__ void row_increases(const T* __restrict__ row, const Hot<NQ>& h, const StreamArgs& a,
-                                              const int32_t phase, const int tick0, const unsigned live,
+                                              const int32_t phase, const int tick0, const bool lane_live,
                                               const bool o1, const bool o2, double (&inc)[kG]) {
     double x[6];
     Tile6<T>::load(row, x);
     double w0 = x[3] - x[0], w1 = x[4] - x[1], w2 = x[5] - x[2];
     const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3], r5 = o2 && x[5] < x[4];
-    // `live`: bit s set when tick s of this thread is evaluated by the fast path; lanes and tick
-    // slots that are not (idle lanes, a partial last group) must never drag the warp into a rare path
-    if (__any_sync(kFull, (r1 | r2 | r3 | r4 | r5) && live)) {   // counter resets are rare (Appendix A step 2)
+    // idle lanes (no ticks, or ticks left to the exact path) must not drag the warp into the rare paths
+    if (__any_sync(kFull, (r1 | r2 | r3 | r4 | r5) && lane_live)) {   // counter resets are rare (Appendix A step 2)
         if (r1) w0 += x[0];
         if (r2) { w0 += x[1]; w1 += x[1]; }
         if (r3) { w0 += x[2]; w1 += x[2]; w2 += x[2]; }
@@ -277,7 +276,10 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
     bool slow[kG];
 #pragma unroll
     for (int s = 0; s < kG; ++s) {
-        slow[s] = !(fst[s] * h.gchk[s] >= res[s]) && ((live >> s) & 1u);
+        // gchk is finite for evaluated ticks, so a NaN product can only come from a NaN sample, for
+        // which the fast formula is already what the exact path gives.  Tick slots this thread does
+        // not evaluate (idle lanes, a partial last group) carry gchk = NaN: never "slow".
+        slow[s] = fst[s] * h.gchk[s] < res[s];
         inc[s] = res[s] * h.f[s];
     }
     if (__any_sync(kFull, slow[0] | slow[1] | slow[2])) {   // rare: a counter that restarted one scrape ago
@@ -438,7 +440,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             // test bounds every time stamp); every division is by a constant (div_const).
             Hot<NQ> h;
             int i0r = 0, i1r = 0;            // unclamped window bounds of tick s = lane (lanes 0..2)
-            double fs = 0.0, gs = INFINITY;
+            double fs = 0.0, gs = 1e300;
             if (lane < kG) {
                 const int t = p.tick0_ms + lane * p.tick_step_ms, lo = t - p.window_ms;
                 i0r = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
@@ -451,7 +453,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                     ext += (d_end < a.thr) ? d_end : a.half_avg;
                     fs = div_const(ext, a.sampled, a.rc_sampled);
                     // an under-estimate of sampled/d_start only sends more rows to the exact path
-                    gs = (a.sampled * (double)__frcp_rd(__double2float_ru(d_start))) * (1.0 - 1e-6);
+                    gs = fmin((a.sampled * (double)__frcp_rd(__double2float_ru(d_start))) * (1.0 - 1e-6), 1e300);
                 }
             }
             int i0s[kG], i1s[kG];
@@ -482,7 +484,9 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                 base = 0;
                 fb_mask = (1u << n_mine) - 1u;
             }
-            const unsigned live = active ? (1u << n_mine) - 1u : 0u;   // ticks the fast path evaluates
+#pragma unroll
+            for (int s = 0; s < kG; ++s)      // tick slots the fast path does not evaluate
+                if (!active || s >= n_mine) { h.f[s] = 0.0; h.gchk[s] = NAN; }
 #pragma unroll
             for (int q = 0; q < kG * NQ; ++q) CG_RECI(q) = -1;
 
@@ -506,7 +510,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll 1
                     for (int k = 0; k < nr; ++k) {
                         double inc[kG];
-                        row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, live, o1, o2, inc);
+                        row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, active, o1, o2, inc);
                         const unsigned role = p.scalar_role[first + k];
 #pragma unroll
                         for (int q = 0; q < 5; ++q)
@@ -550,7 +554,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #pragma unroll 1
                 for (int k = 0; k < nr; ++k) {
                     double inc[kG];
-                    row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, live, o1, o2, inc);
+                    row_increases<T, NQ>(rows + k * pitch + base, h, a, phase, tick0, active, o1, o2, inc);
                     if (!is_inf) {
                         // common case: increases are monotone in the bucket index and below the
                         // search threshold -> prev = inc.  One vote decides whether any lane needs
