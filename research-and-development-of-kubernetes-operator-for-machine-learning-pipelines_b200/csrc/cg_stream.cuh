@@ -263,11 +263,13 @@ __device__ __forceinline__ void row_increases(const T* __restrict__ row, const H
     const bool r1 = x[1] < x[0], r2 = x[2] < x[1], r3 = x[3] < x[2], r4 = x[4] < x[3], r5 = o2 && x[5] < x[4];
     // idle lanes (no ticks, or ticks left to the exact path) must not drag the warp into the rare paths
     if (__any_sync(kFull, (r1 | r2 | r3 | r4 | r5) && lane_live)) {   // counter resets are rare (Appendix A step 2)
-        if (r1) w0 += x[0];
-        if (r2) { w0 += x[1]; w1 += x[1]; }
-        if (r3) { w0 += x[2]; w1 += x[2]; w2 += x[2]; }
-        if (r4) { w1 += x[3]; w2 += x[3]; }
-        if (r5) w2 += x[4];
+        // value before each reset (0 where there is none), added to each window in time order;
+        // adding +0.0 leaves a sum unchanged, so this is the oracle's conditional add
+        const double d1 = r1 ? x[0] : 0.0, d2 = r2 ? x[1] : 0.0, d3 = r3 ? x[2] : 0.0, d4 = r4 ? x[3] : 0.0,
+                     d5 = r5 ? x[4] : 0.0;
+        w0 = ((w0 + d1) + d2) + d3;
+        w1 = ((w1 + d2) + d3) + d4;
+        w2 = ((w2 + d3) + d4) + d5;
     }
     const double res[kG] = {w0, o1 ? w1 : w0, o2 ? w2 : w1};
     const double fst[kG] = {x[0], o1 ? x[1] : x[0], o2 ? x[2] : x[1]};
