@@ -277,7 +277,8 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     if ((rc = check_aligned(scalars, "scalars"))) return rc;
     if ((rc = check_aligned(buckets, "buckets"))) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    if (decisions && path != 1 && stream_eligible(p)) {
+    // per-tick metric output alone (cg_eval_grid) also streams once the grid is worth a CTA
+    if ((decisions || p->n_ticks >= 32) && path != 1 && stream_eligible(p)) {
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
         cg::StreamArgs& a = sp.args;

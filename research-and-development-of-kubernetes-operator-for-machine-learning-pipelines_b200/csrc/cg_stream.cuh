@@ -418,7 +418,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
         if (!hp) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
-            if (tid == 0) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
+            if (tid == 0 && a.decisions) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
             if (a.gate_bits) for (int w = tid; w < n_words; w += n_cons) a.gate_bits[pair * n_words + w] = 0u;
             continue;
         }
@@ -711,7 +711,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         if (last) {
             __threadfence_block();
             if (a.gate_bits) for (int w = lane; w < n_words; w += 32) a.gate_bits[pair * n_words + w] = bits[w];
-            if (lane == 0) {
+            if (lane == 0 && a.decisions) {
                 const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
                 a.decisions[pair] = replay_schedule_bits(bits, n_words, true, st_tick, p);
             }
