@@ -1,0 +1,188 @@
+"""Ingest: Prometheus wire format -> the library's SoA layout.
+
+The reference never sees raw samples: it sends six instant queries per (version, attempt) and
+Prometheus does the arithmetic (mlflow_operator.py:367-411).  The B200 path needs the samples
+themselves, so the step in front of it is one `/api/v1/query_range`-shaped matrix per metric
+name; this module turns those answers into `scalars / buckets / le / phase` arrays plus the
+label index `SeriesStore` uses in place of Prometheus' own.
+
+Label rules are the reference's matchers:
+  seldon_api_executor_server_requests_seconds_count   every series counts toward Q3 (:383);
+      code != "200" also toward Q2 (:375); service == "feedback" also toward Q6 (:410)
+  seldon_api_executor_client_requests_seconds_sum / _count   Q4 / Q5 (:393, :397)
+  seldon_api_executor_client_requests_seconds_bucket  one series per `le`            (:367)
+all selected by (deployment_name, predictor_name, namespace).
+
+Only regular scrape grids are accepted here (sample i at phase + i*period); irregular series
+and stale markers are the next row of SURVEY.md 8(f) and raise `IrregularSeries`.
+"""
+from __future__ import annotations
+
+import json
+import math
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .params import (CgParams, ROLE_CLIENT_COUNT, ROLE_CLIENT_SUM, ROLE_FEEDBACK, ROLE_SERVER_ERROR,
+                     ROLE_SERVER_TOTAL, make_params)
+
+SERVER_COUNT = "seldon_api_executor_server_requests_seconds_count"
+CLIENT_SUM = "seldon_api_executor_client_requests_seconds_sum"
+CLIENT_COUNT = "seldon_api_executor_client_requests_seconds_count"
+CLIENT_BUCKET = "seldon_api_executor_client_requests_seconds_bucket"
+
+
+class IrregularSeries(ValueError):
+    pass
+
+
+def parse_matrix(answer) -> List[Tuple[Dict[str, str], np.ndarray, np.ndarray]]:
+    """One query_range answer (dict or JSON text) -> [(labels, ts_ms int64[], values fp64[])].
+    Prometheus sends sample values as strings ("NaN", "+Inf" included) and times as float seconds."""
+    if isinstance(answer, (str, bytes)):
+        answer = json.loads(answer)
+    if isinstance(answer, dict) and "data" in answer:
+        if answer.get("status", "success") != "success":
+            raise ValueError(f"Prometheus error: {answer.get('error')}")
+        answer = answer["data"]
+    if isinstance(answer, dict):
+        if answer.get("resultType", "matrix") != "matrix":
+            raise ValueError("expected a range-query matrix")
+        answer = answer["result"]
+    out = []
+    for item in answer:
+        vals = item["values"]
+        ts = np.fromiter((int(round(float(t) * 1000.0)) for t, _ in vals), dtype=np.int64, count=len(vals))
+        v = np.fromiter((float(x) for _, x in vals), dtype=np.float64, count=len(vals))
+        out.append((dict(item["metric"]), ts, v))
+    return out
+
+
+def _scalar_role(name: str, labels: Dict[str, str]) -> int:
+    if name == SERVER_COUNT:
+        role = ROLE_SERVER_TOTAL
+        if labels.get("code", "") != "200":
+            role |= ROLE_SERVER_ERROR
+        if labels.get("service", "") == "feedback":
+            role |= ROLE_FEEDBACK
+        return role
+    if name == CLIENT_SUM:
+        return ROLE_CLIENT_SUM
+    if name == CLIENT_COUNT:
+        return ROLE_CLIENT_COUNT
+    raise KeyError(name)
+
+
+def _le_value(text: str) -> float:
+    return math.inf if text in ("+Inf", "Inf", "inf") else float(text)
+
+
+class HostSeries:
+    """What `build_host_batch` returns: the numpy SoA arrays, params and the label index."""
+
+    def __init__(self, scalars, buckets, le, phase, params, index, epoch_ms):
+        self.scalars, self.buckets, self.le, self.phase = scalars, buckets, le, phase
+        self.params, self.index, self.epoch_ms = params, index, epoch_ms
+
+
+def build_host_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str, str], Tuple[str, str]],
+                     period_ms: int = 15000, epoch_ms: Optional[int] = None, dtype: int = 0,
+                     **param_overrides) -> HostSeries:
+    """answers: {metric name: query_range answer}.  versions: {(deployment_name, namespace):
+    (new predictor_name, old predictor_name)}.  Every (pair, version) must expose the same
+    scalar label sets (same K, same roles in the same order after sorting by labels) and the
+    same `le` set, sampled on a regular grid of `period_ms`."""
+    pairs = sorted(versions)
+    row_of = {key: i for i, key in enumerate(pairs)}
+    ver_of = {}
+    for key, (new, old) in versions.items():
+        ver_of[(key, new)] = 0
+        ver_of[(key, old)] = 1
+    scal: Dict[Tuple[int, int], List[Tuple[tuple, int, np.ndarray, np.ndarray]]] = {}
+    buck: Dict[Tuple[int, int], List[Tuple[float, np.ndarray, np.ndarray]]] = {}
+    for name, answer in answers.items():
+        for labels, ts, v in parse_matrix(answer):
+            key = (labels.get("deployment_name", ""), labels.get("namespace", ""))
+            vk = ver_of.get((key, labels.get("predictor_name", "")))
+            if vk is None:
+                continue
+            slot = (row_of[key], vk)
+            if name == CLIENT_BUCKET:
+                buck.setdefault(slot, []).append((_le_value(labels["le"]), ts, v))
+            else:
+                # canonical row order: server counters, client sum, client count; then by labels
+                order = ((SERVER_COUNT, CLIENT_SUM, CLIENT_COUNT).index(name), name,
+                         tuple(sorted((k, x) for k, x in labels.items()
+                                      if k not in ("deployment_name", "namespace", "predictor_name"))))
+                scal.setdefault(slot, []).append((order, _scalar_role(name, labels), ts, v))
+    n = len(pairs)
+    if n == 0:
+        raise ValueError("no model pairs")
+    all_ts = [ts for group in list(scal.values()) + list(buck.values()) for item in group for ts in [item[-2]]]
+    if not all_ts:
+        raise ValueError("no series matched")
+    if epoch_ms is None:
+        epoch_ms = int(min(ts[0] for ts in all_ts if len(ts)))
+    T = max(len(ts) for ts in all_ts)
+    roles_ref, le_ref = None, None
+    K = max((len(g) for g in scal.values()), default=0)
+    B = max((len(g) for g in buck.values()), default=0)
+    dt = np.float32 if dtype == 1 else np.float64
+    scalars = np.zeros((n, 2, K, T), dtype=dt)
+    buckets = np.zeros((n, 2, B, T), dtype=dt)
+    phase = np.zeros((n, 2), dtype=np.int32)
+
+    def grid_phase(ts, what):
+        if len(ts) != T:
+            raise IrregularSeries(f"{what}: {len(ts)} samples, expected {T}")
+        if T > 1 and not np.all(np.diff(ts) == period_ms):
+            raise IrregularSeries(f"{what}: samples are not {period_ms} ms apart")
+        return int(ts[0] - epoch_ms)
+
+    for i in range(n):
+        for v in range(2):
+            ph = None
+            group = sorted(scal.get((i, v), []), key=lambda it: it[0])
+            if len(group) != K:
+                raise ValueError(f"pair {pairs[i]} version {v}: {len(group)} scalar series, expected {K}")
+            roles = tuple(g[1] for g in group)
+            roles_ref = roles if roles_ref is None else roles_ref
+            if roles != roles_ref:
+                raise ValueError(f"pair {pairs[i]} version {v}: scalar label sets differ from the first pair's")
+            for k, (order, role, ts, vals) in enumerate(group):
+                p0 = grid_phase(ts, f"{pairs[i]} v{v} {order[1]}")
+                ph = p0 if ph is None else ph
+                if p0 != ph:
+                    raise IrregularSeries(f"{pairs[i]} v{v}: series of one target are scraped at different times")
+                scalars[i, v, k] = vals
+            hist = sorted(buck.get((i, v), []), key=lambda it: it[0])
+            if len(hist) != B:
+                raise ValueError(f"pair {pairs[i]} version {v}: {len(hist)} buckets, expected {B}")
+            les = np.array([h[0] for h in hist], dtype=np.float64)
+            le_ref = les if le_ref is None else le_ref
+            if B and not np.array_equal(les, le_ref):
+                raise ValueError(f"pair {pairs[i]} version {v}: `le` set differs from the first pair's")
+            for b, (_, ts, vals) in enumerate(hist):
+                p0 = grid_phase(ts, f"{pairs[i]} v{v} le={les[b]}")
+                ph = p0 if ph is None else ph
+                if p0 != ph:
+                    raise IrregularSeries(f"{pairs[i]} v{v}: series of one target are scraped at different times")
+                buckets[i, v, b] = vals
+            phase[i, v] = 0 if ph is None else ph
+    params = make_params(n_samples=T, n_scalar=K, n_buckets=B, roles=roles_ref, period_ms=period_ms,
+                         dtype=dtype, **param_overrides)
+    if params.row_pitch * params.elem_bytes % 16:
+        pitch = -(-T * params.elem_bytes // 16) * 16 // params.elem_bytes
+        pad = lambda a: np.concatenate([a, np.zeros(a.shape[:-1] + (pitch - T,), a.dtype)], axis=-1)  # noqa: E731
+        scalars, buckets = np.ascontiguousarray(pad(scalars)), np.ascontiguousarray(pad(buckets))
+        params = make_params(n_samples=T, n_scalar=K, n_buckets=B, roles=roles_ref, period_ms=period_ms,
+                             dtype=dtype, row_pitch=pitch, **param_overrides)
+    index = {key: (row_of[key], {versions[key][0]: 0, versions[key][1]: 1}) for key in pairs}
+    return HostSeries(scalars, buckets, le_ref if le_ref is not None else np.zeros(0), phase, params, index, epoch_ms)
+
+
+def to_store(host: HostSeries, device="cuda", now_ms: Optional[int] = None):
+    """Upload an ingested batch to the GPU as an operator_api.SeriesStore."""
+    from .operator_api import SeriesStore
+    return SeriesStore.from_host(host, device=device, index=host.index, now_ms=now_ms)

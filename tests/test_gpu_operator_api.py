@@ -91,3 +91,24 @@ def test_batched_api_and_patch_batch():
     patches = api.decisions_to_predictor_traffic(dec, ["2"] * len(d), ["1"] * len(d))
     for i, run in runs.items():
         assert [p["traffic"] for p in patches[i]["predictors"]] == run["weights"][-1]
+
+
+def test_ingested_prometheus_answers_drive_the_same_decisions():
+    """Wire format -> ingest -> SeriesStore -> the drop-in signatures and the batched API."""
+    from canary_b200 import ingest
+    from test_ingest import render
+    b = BATCHES["small"]
+    wire, versions, epoch = render(b)
+    host = ingest.build_host_batch(wire, versions, period_ms=b.params.period_ms, epoch_ms=epoch)
+    store = ingest.to_store(host)
+    dec = api.evaluate_canaries(store).cpu().numpy()
+    for case in CASES:
+        if case["geometry"] != "small":
+            continue
+        i, run = case["pair"], case["runs"][0]
+        assert tuple(dec[i, :5]) == (run["cur"], run["prev"], run["state"], run["n_promotions"], run["n_evals"])
+        t = case["ticks"][1]
+        store.set_time(host.params.tick0_ms + t["tick"] * host.params.tick_step_ms)
+        got = api.get_model_metrics(store, f"model-{i:03d}", "v2", "prod")
+        for k, v in t["new"].items():
+            assert same_float(got[k], fdec(v)), (i, k)
