@@ -3,25 +3,32 @@
 // mlflow_operator.py:363, :294 with Prometheus' usual 15 s scrapes).
 //
 // Layout of the work
-//   * One CTA = CW consumer warps + 1 producer warp, persistent over model pairs.
-//   * The producer's elected lane streams series ROWS through a shared-memory ring with
-//     the TMA bulk-copy engine (cp.async.bulk + mbarrier complete_tx): per (pair,
-//     version) the K scalar rows, then the +Inf bucket row, then bucket rows 0..B-2 in
-//     groups of 4.  Every sample is read from HBM exactly once; the ring keeps several
-//     KB per CTA in flight so the copy engine never waits for the math.
-//   * A consumer thread owns one PERIOD of the tick grid: 3 consecutive ticks whose
-//     4-sample windows live in 6 consecutive samples (three 128-bit shared loads per
-//     row).  Which of the 6 each tick uses depends only on the series phase, so it is a
-//     CTA-uniform pattern (O1, O2) and the row loop is instantiated per pattern.
-//   * Per row and tick: reset-aware window delta, zero-point-clamp test, extrapolation
-//     factor, then the histogram search state (first bucket reaching the rank) and a
-//     monotonicity flag.  After the last row each thread finishes histogram_quantile,
-//     the derived ratios (:387-404) and, once both versions are done, the gate
-//     (:419-460).  Gate bits are OR-ed into shared memory and thread 0 replays the step
-//     loop (:296-361).
-//   * Anything the fast path cannot decide exactly (series edges, coincident phases,
-//     non-monotonic bucket rates, a search landing within an ulp of the rank) is
-//     re-evaluated for that tick by the whole warp from global memory with the plain
+//   * One CTA = 4 warps, 4 CTAs per SM, persistent over model pairs.  Every warp is a consumer;
+//     there is no producer warp.
+//   * Series ROWS stream through a shared-memory ring filled by the TMA bulk-copy engine
+//     (cp.async.bulk + mbarrier complete_tx).  The warp that leaves a ring slot last issues the
+//     fill that comes n_slots later in the stream, so nobody polls for free slots.  Order per
+//     (pair, version): the K scalar rows, the +Inf bucket row, then bucket rows 0..B-2 in
+//     groups of 4.  Every sample is read from HBM exactly once.
+//   * A thread owns one PERIOD of the tick grid: 3 consecutive ticks whose 4-sample windows live
+//     in 6 consecutive samples (three 128-bit shared loads per row).  Which of the 6 each tick
+//     uses depends only on the series phase: a warp-uniform pattern.  Because 3 tick steps are
+//     exactly 2 scrape periods, the extrapolation terms depend on the tick slot alone and are
+//     computed once per (pair, version) by three lanes.
+//   * Per row: window deltas with reset corrections, a one-multiply proof that the zero-point
+//     clamp cannot fire, increase = result * f; for bucket rows the monotonic fix as a running
+//     max and the search for the rank in increase space.  Each rare event (a reset in the tile,
+//     a possible clamp, a thread reaching its rank or needing the fix) is one warp vote, so the
+//     common path is straight-line.  After the last row each thread finishes
+//     histogram_quantile, the ratios (:387-404) and, once both versions are done, the gate
+//     (:419-460); gate bits are OR-ed into shared memory and the warp that finishes a pair last
+//     replays the step loop (:296-361).
+//   * Registers hold only what every row touches; everything else is a shared-memory record per
+//     thread (L1 is too small to back local arrays once the rings take their share), and code
+//     that runs once per (pair, version) is kept compact and out of line for the instruction cache.
+//   * Anything the fast path cannot decide exactly (series edges, phases that put a sample on a
+//     window edge, a mis-speculated observation count, a search landing within an ulp of the
+//     rank) is re-evaluated for that tick by the whole warp from global memory with the plain
 //     sequential semantics (coop_eval_tick).  Results are bit-identical either way.
 #pragma once
 #include "cg_math.cuh"
