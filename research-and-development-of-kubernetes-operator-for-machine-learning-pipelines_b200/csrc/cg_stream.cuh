@@ -598,7 +598,8 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                             CG_REC(R::kObs + s) = inc[s];
                             const double obs = div_const(inc[s], a.range_s, a.rc_range);
 #pragma unroll
-                            for (int q = 0; q < NQ; ++q) h.x0[s][q] = active ? (p.q[q] * obs) * a.range_s : NAN;
+                            for (int q = 0; q < NQ; ++q)   // a candidate threshold; the finish confirms it in rate space
+                                h.x0[s][q] = active ? fmin((p.q[q] * obs) * a.range_s, inc[s]) : NAN;
                         }
                     }
                 }
@@ -616,7 +617,12 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                 // observations after the monotonic fix; the search assumed the +Inf bucket itself
                 unsigned spec_bad = 0;
 #pragma unroll
-                for (int s = 0; s < kG; ++s) if (CG_REC(R::kObs + s) < h.prev[s]) spec_bad |= 1u << s;
+                for (int s = 0; s < kG; ++s) {
+                    if (CG_REC(R::kObs + s) < h.prev[s]) spec_bad |= 1u << s;
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q)     // search never fired: remember the largest fixed count
+                        if (CG_RECI(s * NQ + q) < 0) CG_REC(R::kCprev + s * NQ + q) = h.prev[s];
+                }
 #pragma unroll 1
                 for (int s = 0; s < n_mine; ++s) {
                     const double obs_inc = CG_REC(R::kObs + s);
@@ -635,7 +641,8 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         const double cc = bb > 0 ? cbr - cpr : cbr, rk = bb > 0 ? rank - cpr : rank;
                         const double interp = start + (end - start) * ddiv_call(rk, cc);
                         // the search ran in increase space; confirm it in rate space
-                        const bool confirmed = (cbr >= rank) && (bb <= 0 || cpr < rank);
+                        // (no bucket reached the threshold: then none below the +Inf one may reach the rank)
+                        const bool confirmed = bb < 0 ? (cpr < rank) : ((cbr >= rank) && (bb == 0 || cpr < rank));
                         const bool q_ok = !isnan(qq) && qq >= 0 && qq <= 1;
                         const bool searched = q_ok && shape_ok && obs != 0;
                         double r = interp;
@@ -644,7 +651,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
                         if (!searched) r = NAN;                       // bad shape, q is NaN, or no observations
                         if (qq < 0) r = -INFINITY;
                         if (qq > 1) r = INFINITY;
-                        if (searched && (!spec_ok || (bb >= 0 && !confirmed))) fb_mask |= 1u << s;
+                        if (searched && (!spec_ok || !confirmed)) fb_mask |= 1u << s;
                         if (q == p.gate_q) CG_REC(R::kQv + s) = r;
                         if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick0 + s) * W + q] = r;
                     }

@@ -111,12 +111,21 @@ CONFIGS = {
                                              tick_step_ms=10000), n=40, gen={}),
     "short_series": dict(make=dict(n_samples=6, n_buckets=4, n_ticks=40), n=17, gen=dict(resets=False)),
     "one_sample": dict(make=dict(n_samples=2, row_pitch=2, n_buckets=2, n_ticks=12), n=5, gen=dict(resets=False)),
+    # streaming-kernel corner cases
+    "single_bucket": dict(make=dict(n_samples=60, n_buckets=1), n=20, gen={}),
+    "two_buckets": dict(make=dict(n_samples=60, n_buckets=2), n=20, gen={}),
+    "k16_b64": dict(make=dict(n_samples=48, n_scalar=16, n_buckets=64,
+                              roles=[1, 3, 4, 8] + [1, 3, 17, 19] * 3), n=12, gen=dict(adversarial=0.2)),
+    "odd_tick0": dict(make=dict(n_samples=100, n_buckets=8, tick0_ms=75000), n=24, gen={}),
+    "late_tick0_many_ticks": dict(make=dict(n_samples=240, n_buckets=6, tick0_ms=45000, n_ticks=400), n=10, gen={}),
+    "q_edges": dict(make=dict(n_samples=60, n_buckets=8, quantiles=(0.0, 1.0, -0.5, 1.5), gate_q=1), n=16, gen={}),
 }
 
 
 # geometries the streaming kernel covers (window = 4 periods, tick step = 2/3 period)
 STREAMING = {"cfg2_error_rate_only", "cfg3_quantiles", "cfg4_full_resets", "k5_feedback_b12",
-             "left_open_coincident", "closed_coincident", "ragged_pitch", "short_series"}
+             "left_open_coincident", "closed_coincident", "ragged_pitch", "short_series",
+             "single_bucket", "two_buckets", "k16_b64", "odd_tick0", "late_tick0_many_ticks", "q_edges"}
 
 
 @pytest.mark.parametrize("name", sorted(CONFIGS))
