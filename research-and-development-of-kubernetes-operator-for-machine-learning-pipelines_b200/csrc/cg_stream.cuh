@@ -123,8 +123,8 @@ static __device__ __noinline__ double extrapolate_call(double result, double fir
 }
 
 // ---- warp-cooperative exact evaluation of one (pair, version, tick) from global memory
-template <typename T>
-__device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int32_t phase, int tick, int lane,
+template <typename T, typename Args>
+__device__ __noinline__ void coop_eval_tick(const Args& a, int64_t pv, int32_t phase, int tick, int lane,
                                const double* __restrict__ s_le, double* m, uint8_t& valid_out) {
     const cg_params& p = a.p;
     const int nq = p.n_q, K = p.n_scalar, B = p.n_buckets;
