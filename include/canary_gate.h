@@ -200,8 +200,7 @@ int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const
                        int64_t n_pairs, const cg_params* p, cg_decision* decisions,
                        uint32_t* gate_bits, double* metrics, uint8_t* valid, void* stream);
 
-/* Which streaming kernels cover these params: bit 0 = the streaming kernel (path 2),
- * bit 1 = the pair-parallel streaming kernel (path 3); 0 = only the general kernel. */
+/* 1 if cg_eval_fused would take the streaming kernel for these params, else 0. */
 int cg_stream_eligible(const cg_params* p);
 
 /* Launch geometry the library would use (for reporting): CTAs, threads, dynamic smem. */

@@ -18,7 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcanarygate.so")
-HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_stream.cuh", "cg_pairstream.cuh", "cg_synth.cuh",
+HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_stream.cuh", "cg_synth.cuh",
            os.path.join(ROOT, "include", "canary_gate.h")]
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -31,15 +31,9 @@ def _units():
         for nq in (1, 2, 3, 4):
             name = f"cg_launch_stream_{tchar}{nq}"
             defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]
-            # developer aid: in-kernel phase timers, CG_TIMING=stream or CG_TIMING=pair
-            if os.environ.get("CG_TIMING") == "stream" and name == "cg_launch_stream_d1":
-                defs += ["-DCG_TIMING", "-DCG_TIMING_EXPORT"]
+            if os.environ.get("CG_TIMING") and name == "cg_launch_stream_d1":
+                defs += ["-DCG_TIMING", "-DCG_TIMING_EXPORT"]    # developer aid: in-kernel phase timers (tools/profile_kernel.py)
             units.append((name, "cg_stream_inst.cu", defs))
-            pname = f"cg_launch_pair_{tchar}{nq}"
-            pdefs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={pname}"]
-            if os.environ.get("CG_TIMING") == "pair" and pname == "cg_launch_pair_d1":
-                pdefs += ["-DCG_TIMING", "-DCG_TIMING_EXPORT"]
-            units.append((pname, "cg_pair_inst.cu", pdefs))
     return units
 
 
@@ -80,7 +74,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         res = subprocess.run(cmd, capture_output=True, text=True)
         return obj, res.returncode, " ".join(cmd) + "\n" + res.stdout + res.stderr
 
-    with ThreadPoolExecutor(max_workers=min(17, os.cpu_count() or 1)) as ex:
+    with ThreadPoolExecutor(max_workers=min(9, os.cpu_count() or 1)) as ex:
         results = list(ex.map(compile_one, _units()))
     objs = []
     for obj, rc, log in results:

@@ -11,7 +11,6 @@
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
 #include "cg_stream.cuh"
-#include "cg_pairstream.cuh"
 #include "cg_synth.cuh"
 
 namespace {
@@ -210,120 +209,13 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     return CG_OK;
 }
 
-
-// ---- pair-parallel streaming kernel (cg_pairstream.cuh) --------------------------------
-struct PairPlan {
-    cg::PairArgs args;
-    int grid;
-};
-
-int rec6_doubles(int n_q) {
-    switch (n_q <= 1 ? 1 : n_q) {
-        case 1: return cg::Rec6<1>::kDoubles;
-        case 2: return cg::Rec6<2>::kDoubles;
-        case 3: return cg::Rec6<3>::kDoubles;
-        default: return cg::Rec6<4>::kDoubles;
-    }
-}
-
-int pair_slot_uses(const cg_params* p) {
-    const int r = cg::kRowsPerVer;
-    return (p->n_scalar + r - 1) / r + (p->n_buckets > 0 ? 1 + (p->n_buckets - 1 + r - 1) / r : 0);
-}
-
-size_t pair_fixed_smem(const cg_params* p) {
-    const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
-    return (size_t)p->n_buckets * 8 + (n_words + 1) * 4 + 32 * 12 + 256 +
-           (size_t)2 * cg::kHalf * rec6_doubles(p->n_q) * 8 + (size_t)2 * cg::kHalf * cg::kP6 * (3 * 8 + 1);
-}
-
-bool pair_eligible(const cg_params* p) {
-    if (!stream_eligible(p)) return false;
-    if (p->n_ticks < 2 * cg::kG) return false;
-    // threads per version: pairs of full periods, one more for a partial last period
-    const int n_per = (p->n_ticks + cg::kG - 1) / cg::kG, rem = p->n_ticks % cg::kG;
-    const int n_fullp = rem ? n_per - 1 : n_per;
-    if ((n_fullp + 1) / 2 + (rem ? 1 : 0) > cg::kHalf) return false;
-    if (pair_slot_uses(p) < 4) return false;      // warps of a CTA must stay within one pair of each other
-    const size_t slot = (size_t)2 * cg::kRowsPerVer * p->row_pitch * elem_size(p);
-    return 3 * slot + pair_fixed_smem(p) <= (size_t)kMaxSmem;
-}
-
-int plan_pair(const cg_params* p, int64_t n_pairs, PairPlan* plan) {
-    cg::PairArgs& a = plan->args;
-    memset(&a, 0, sizeof(a));
-    a.p = *p;
-    a.n_pairs = n_pairs;
-    a.slot_bytes = (uint32_t)((size_t)2 * cg::kRowsPerVer * p->row_pitch * elem_size(p));
-    const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
-    a.range_s = (double)p->window_ms / 1000.0;
-    a.rc_range = 1.0 / a.range_s;
-    a.sampled = (double)(3 * (int64_t)p->period_ms) / 1000.0;
-    a.rc_sampled = 1.0 / a.sampled;
-    {
-        const double avg = a.sampled / 3.0;     // sampled / (n - 1), n = 4
-        a.thr = avg * 1.1;
-        a.half_avg = avg / 2;
-    }
-    const size_t rec = (size_t)2 * cg::kHalf * rec6_doubles(p->n_q) * 8;
-    const size_t xchg = (size_t)2 * cg::kHalf * cg::kP6 * (3 * 8 + 1);
-    const size_t fixed = pair_fixed_smem(p);
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int per_sm = 1, slots = 0;
-    int c_max = 3;
-    if (const char* e = getenv("CG_PAIR_PER_SM")) { int v = atoi(e); if (v >= 1 && v <= 3) c_max = v; }   // tuning aid
-    for (int c = c_max; c >= 1; --c) {
-        const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
-        if (budget <= fixed) continue;
-        const int sl = (int)((budget - fixed) / a.slot_bytes);
-        if (sl >= 3) { per_sm = c; slots = sl; break; }
-    }
-    if (slots < 3) return fail(CG_EINVAL, "pair kernel: ring does not fit shared memory");
-    const int uses = pair_slot_uses(p);
-    if (slots > uses - 1) slots = uses - 1;
-    if (slots > 16) slots = 16;
-    if (const char* e = getenv("CG_STREAM_SLOTS")) { int v = atoi(e); if (v >= 3 && v < slots) slots = v; }   // tuning aid
-    a.n_slots = slots;
-    size_t off = (size_t)slots * a.slot_bytes;
-    a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
-    a.off_bits = (uint32_t)off; off += (n_words + 1) * 4;
-    off = (off + 7) & ~(size_t)7;
-    a.off_bars = (uint32_t)off; off += (size_t)slots * 8 + (size_t)slots * 4;
-    off = (off + 15) & ~(size_t)15;
-    a.off_rec = (uint32_t)off;  off += rec;
-    a.off_xchg = (uint32_t)off; off += xchg;
-    a.smem_bytes = (uint32_t)off;
-    int64_t g = (int64_t)sms * per_sm;
-    if (g > n_pairs) g = n_pairs;
-    if (g < 1) g = 1;
-    plan->grid = (int)g;
-    return CG_OK;
-}
-
 }  // namespace
 // one per translation unit cg_stream_inst.cu (see build.py)
 #define CG_DECL_INST(n) cudaError_t n(const cg::StreamArgs&, int, int, int, cudaStream_t)
 CG_DECL_INST(cg_launch_stream_d1); CG_DECL_INST(cg_launch_stream_d2); CG_DECL_INST(cg_launch_stream_d3);
 CG_DECL_INST(cg_launch_stream_d4); CG_DECL_INST(cg_launch_stream_f1); CG_DECL_INST(cg_launch_stream_f2);
 CG_DECL_INST(cg_launch_stream_f3); CG_DECL_INST(cg_launch_stream_f4);
-#define CG_DECL_PAIR(n) cudaError_t n(const cg::PairArgs&, int, cudaStream_t)
-CG_DECL_PAIR(cg_launch_pair_d1); CG_DECL_PAIR(cg_launch_pair_d2); CG_DECL_PAIR(cg_launch_pair_d3);
-CG_DECL_PAIR(cg_launch_pair_d4); CG_DECL_PAIR(cg_launch_pair_f1); CG_DECL_PAIR(cg_launch_pair_f2);
-CG_DECL_PAIR(cg_launch_pair_f3); CG_DECL_PAIR(cg_launch_pair_f4);
 namespace {
-
-int launch_pair(const PairPlan& plan, cudaStream_t s) {
-    typedef cudaError_t (*fn_t)(const cg::PairArgs&, int, cudaStream_t);
-    static const fn_t table[2][4] = {
-        {cg_launch_pair_d1, cg_launch_pair_d2, cg_launch_pair_d3, cg_launch_pair_d4},
-        {cg_launch_pair_f1, cg_launch_pair_f2, cg_launch_pair_f3, cg_launch_pair_f4}};
-    int nq = plan.args.p.n_q < 1 ? 1 : plan.args.p.n_q;
-    const cudaError_t e = table[plan.args.p.dtype == CG_F32 ? 1 : 0][nq - 1](plan.args, plan.grid, s);
-    if (e != cudaSuccess) return cuda_fail(e, "launch pair_kernel");
-    g_launches.fetch_add(1);
-    return CG_OK;
-}
 
 int launch_stream(const StreamPlan& plan, cudaStream_t s) {
     typedef cudaError_t (*fn_t)(const cg::StreamArgs&, int, int, int, cudaStream_t);
@@ -386,16 +278,6 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     if ((rc = check_aligned(buckets, "buckets"))) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     // per-tick metric output alone (cg_eval_grid) also streams once the grid is worth a CTA
-    if (decisions && (path == 3 || (path == 0 && getenv("CG_PAIR_KERNEL"))) && pair_eligible(p)) {
-        PairPlan pp;
-        if ((rc = plan_pair(p, n_pairs, &pp))) return rc;
-        cg::PairArgs& a = pp.args;
-        a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
-        a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
-        a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
-        return launch_pair(pp, s);
-    }
-    if (path == 3) return fail(CG_EINVAL, "geometry not covered by the pair-parallel streaming kernel");
     if ((decisions || p->n_ticks >= 32) && path != 1 && stream_eligible(p)) {
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
@@ -478,14 +360,14 @@ int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const
                        int64_t n_pairs, const cg_params* p, cg_decision* decisions, uint32_t* gate_bits,
                        double* metrics, uint8_t* valid, void* stream) {
     if (n_pairs > 0 && !decisions) return fail(CG_EINVAL, "decisions is NULL");
-    if (path < 0 || path > 3) return fail(CG_EINVAL, "path must be 0 (auto), 1 (general), 2 (streaming) or 3 (pair-parallel streaming)");
+    if (path < 0 || path > 2) return fail(CG_EINVAL, "path must be 0 (auto), 1 (general) or 2 (streaming)");
     return run_general(scalars, buckets, le, phase, has_previous, start_tick, n_pairs, p, decisions,
                        gate_bits, metrics, valid, stream, path);
 }
 
 int cg_stream_eligible(const cg_params* p) {
     if (check_params(p)) return 0;
-    return (stream_eligible(p) ? 1 : 0) | (pair_eligible(p) ? 2 : 0);
+    return stream_eligible(p) ? 1 : 0;
 }
 
 int cg_gate(const double* new_m, const uint8_t* new_v, const double* old_m, const uint8_t* old_v,

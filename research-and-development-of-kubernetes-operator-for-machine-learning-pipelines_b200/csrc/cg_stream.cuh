@@ -123,8 +123,8 @@ static __device__ __noinline__ double extrapolate_call(double result, double fir
 }
 
 // ---- warp-cooperative exact evaluation of one (pair, version, tick) from global memory
-template <typename T, typename Args>
-__device__ __noinline__ void coop_eval_tick(const Args& a, int64_t pv, int32_t phase, int tick, int lane,
+template <typename T>
+__device__ __noinline__ void coop_eval_tick(const StreamArgs& a, int64_t pv, int32_t phase, int tick, int lane,
                                const double* __restrict__ s_le, double* m, uint8_t& valid_out) {
     const cg_params& p = a.p;
     const int nq = p.n_q, K = p.n_scalar, B = p.n_buckets;
@@ -387,16 +387,15 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
 #define CG_REC(f) rec[(f) * n_cons]
 #define CG_RECI(f) rec_i[(f) * n_cons]        // ints: [0, kG*NQ) bstar, kG*NQ valid bytes, kG*NQ+1 stash valid bytes
     const int pitch = p.row_pitch;
-    uint32_t it = 0;
+    uint32_t slot = 0, ring_phase = 0;         // position in the ring and the parity of its mbarrier
     int bit_buf = 0;                           // which of the 3 gate-bit buffers this pair uses
 
 #ifdef CG_TIMING
     long long t_acq = 0;
 #endif
     auto acquire = [&]() -> const T* {
-        const uint32_t slot = it % (uint32_t)a.n_slots;
         CG_T(tw0);
-        mbar_wait(full_bar + slot, (it / (uint32_t)a.n_slots) & 1u);
+        mbar_wait(full_bar + slot, ring_phase);
 #ifdef CG_TIMING
         t_acq = clock64();
         CG_TADD(0, t_acq - tw0);
@@ -404,7 +403,6 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
         return reinterpret_cast<const T*>(ring + (size_t)slot * a.slot_bytes);
     };
     auto release = [&]() {
-        const uint32_t slot = it % (uint32_t)a.n_slots;
         __syncwarp();
 #ifdef CG_TIMING
         CG_TADD(1, clock64() - t_acq);
@@ -417,7 +415,7 @@ stream_kernel(const __grid_constant__ StreamArgs a) {
             }
         }
         cursor_next(fill);
-        ++it;
+        if (++slot == (uint32_t)a.n_slots) { slot = 0; ring_phase ^= 1u; }   // no division in the row stream
     };
     CG_T(tk0);
 

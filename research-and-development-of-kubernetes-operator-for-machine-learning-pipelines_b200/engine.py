@@ -101,8 +101,7 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
                want_bits: bool = False, want_metrics: bool = False, out=None, path: int = 0):
     """metrics -> gate -> step loop in one pass over the series (mlflow_operator.py:302-317
     for every MlflowModel at once).  -> decisions [N, 6] int32 (+ gate_bits, metrics, valid).
-    path: 0 = let the library choose, 1 = general kernel, 2 = streaming kernel,
-    3 = pair-parallel streaming kernel."""
+    path: 0 = let the library choose, 1 = general kernel, 2 = streaming kernel."""
     n = _check_series(scalars, buckets, le, phase, p)
     dev = phase.device
     if has_previous is not None:
@@ -133,12 +132,7 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
 
 def stream_eligible(p: CgParams) -> bool:
     """True if cg_eval_fused takes the streaming kernel for these params."""
-    return bool(_lib.lib.cg_stream_eligible(C.byref(p)) & 1)
-
-
-def pair_eligible(p: CgParams) -> bool:
-    """True if the pair-parallel streaming kernel (path 3) covers these params."""
-    return bool(_lib.lib.cg_stream_eligible(C.byref(p)) & 2)
+    return bool(_lib.lib.cg_stream_eligible(C.byref(p)))
 
 
 def synth_fill(n_pairs: int, p: CgParams, le: torch.Tensor, seed: int = 0xC0FFEE, pair_offset: int = 0,

@@ -128,10 +128,6 @@ STREAMING = {"cfg2_error_rate_only", "cfg3_quantiles", "cfg4_full_resets", "k5_f
              "single_bucket", "two_buckets", "k16_b64", "odd_tick0", "late_tick0_many_ticks", "q_edges"}
 
 
-# ... of which the pair-parallel kernel covers those with 6..381 ticks and at least 4 ring slot uses
-PAIR = STREAMING - {"late_tick0_many_ticks", "cfg2_error_rate_only", "single_bucket"}
-
-
 @pytest.mark.parametrize("name", sorted(CONFIGS))
 def test_seeded_batch_matches_oracle(name):
     cfg = CONFIGS[name]
@@ -141,8 +137,7 @@ def test_seeded_batch_matches_oracle(name):
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what=name)
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    paths = [1] + ([2] if engine.stream_eligible(p) else []) + ([3] if engine.pair_eligible(p) else [])
-    assert engine.pair_eligible(p) == (name in PAIR), name
+    paths = [1, 2] if engine.stream_eligible(p) else [1]
     assert engine.stream_eligible(p) == (name in STREAMING), name
     for path in paths:
         got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
@@ -159,7 +154,7 @@ def test_fp32_storage_matches_oracle_on_rounded_inputs():
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what="fp32")
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    for path in (1, 2, 3):
+    for path in (1, 2):
         got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
         assert np.array_equal(got_bits, want_bits) and np.array_equal(got_dec, want_dec)
         assert_metrics_match(m2, want_m, v2, want_v, rtol=1e-6, exact=True, what=f"fp32 path {path}")
@@ -172,7 +167,7 @@ def test_start_ticks_has_previous_and_running_out_of_data():
     st = rng.integers(0, p.n_ticks + 5, size=50).astype(np.int32)
     hp = (rng.random(50) < 0.8).astype(np.uint8)
     want, _ = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, has_previous=hp, start_tick=st)
-    for path in (1, 2, 3):
+    for path in (1, 2):
         got, _ = gpu_fused(b, has_previous=hp, start_tick=st, path=path)
         assert np.array_equal(got, want), path
     assert (got[hp == 0, 2] == P.STATE_NO_CANARY).all()

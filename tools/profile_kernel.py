@@ -32,12 +32,8 @@ if os.environ.get("CG_TIMING"):
     from canary_b200 import _lib
     buf = (C.c_ulonglong * 16)()
     _lib.lib.cg_debug_timing(buf, 1)
-    if os.environ["CG_TIMING"] == "pair":
-        names = ["wait_new", "wait_old", "rows_new(+wait)", "rows_old(+wait)", "setup", "finish", "fallback", "gate", "total", "warps", "bucket_rows", "ev_slow", "ev_neg", "ev_mono", "ev_rank", "ev_any"]
-        ti = 8
-    else:
-        names = ["wait_full", "rows", "setup", "finish", "barrier", "total", "warps", "coop_calls", "finish_quantile", "finish_fallback", "-", "-", "-", "-", "-", "-"]
-        ti = 5
+    names = ["wait_full", "rows", "setup", "finish", "barrier", "total", "warps", "coop_calls", "finish_quantile", "finish_fallback", "-", "-", "-", "-", "-", "-"]
+    ti = 5
     vals = list(buf)
     tot = vals[ti] or 1
     print("warp-cycles over all launches:", {n: f"{v:.3e} ({100 * v / tot:.1f}%)" for n, v in zip(names, vals)})
