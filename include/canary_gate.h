@@ -184,6 +184,24 @@ int cg_eval_fused(const void* scalars, const void* buckets, const double* le,
                   cg_decision* decisions, uint32_t* gate_bits,
                   double* metrics, uint8_t* valid, void* stream);
 
+/* The same fused step for IRREGULAR series: every series has its own time
+ * stamps and its own number of samples -- jittered or missed scrapes, series that start late or
+ * end early.  Stale markers must already be dropped, as Prometheus drops them from range vectors
+ * (canary_b200.ingest does it).  A series with fewer than 2 samples in a window yields no output
+ * for that tick; a bucket without output is absent from the vector histogram_quantile sees.
+ *   scalars / buckets        values, laid out as for cg_eval_fused (only the first cnt samples of a row count)
+ *   ts_scalars / ts_buckets  [n_pairs][2][K|B][row_pitch] int32 ms, strictly increasing within a row,
+ *                            same epoch as tick0_ms; 16-byte aligned; row_pitch a multiple of 4
+ *   cnt_scalars/ cnt_buckets [n_pairs][2][K|B] int32 samples present (0..n_samples)
+ * period_ms is ignored.  Outputs as in cg_eval_fused (any may be NULL, not all).
+ * Replaces :302-317 against a Prometheus whose scrapes are not a perfect grid. */
+int cg_eval_irregular(const void* scalars, const void* buckets, const int32_t* ts_scalars,
+                      const int32_t* ts_buckets, const int32_t* cnt_scalars,
+                      const int32_t* cnt_buckets, const double* le, const uint8_t* has_previous,
+                      const int32_t* start_tick, int64_t n_pairs, const cg_params* p,
+                      cg_decision* decisions, uint32_t* gate_bits, double* metrics,
+                      uint8_t* valid, void* stream);
+
 /* Benchmark / test utility with no counterpart in the reference: fill device arrays with
  * seeded synthetic series (SURVEY.md 8(d) model).  Values are a pure function of
  * (seed, pair_offset + local pair, version, series, sample), so shards agree. */

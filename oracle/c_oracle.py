@@ -43,6 +43,7 @@ def lib():
         _lib.cgo_eval_fused.argtypes = [C.c_void_p] * 6 + [C.c_int64, C.c_void_p, C.c_void_p,
                                                            C.c_void_p, C.c_int]
         _lib.cgo_eval_lazy.argtypes = [C.c_void_p] * 6 + [C.c_int64, C.c_void_p, C.c_void_p, C.c_int]
+        _lib.cgo_eval_irregular.argtypes = [C.c_void_p] * 9 + [C.c_int64] + [C.c_void_p] * 5 + [C.c_int]
     return _lib
 
 
@@ -123,3 +124,20 @@ def eval_lazy(scalars, buckets, le, phase, p, has_previous=None, start_tick=None
                              _ptr(has_previous), _ptr(start_tick), n_pairs, C.byref(p),
                              _ptr(dec), n_threads), "eval_lazy")
     return dec
+
+
+def eval_irregular(scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, p,
+                   has_previous=None, start_tick=None, n_threads=1, want_metrics=False):
+    """Irregular series (per-series int32 ms time stamps + sample counts): decisions, gate bits and,
+    on request, the per-tick metric records."""
+    n_pairs = cnt_scalars.shape[0]
+    dec = np.empty((n_pairs, 6), dtype=np.int32)
+    bits = np.zeros((n_pairs, (p.n_ticks + 31) // 32), dtype=np.uint32)
+    W = p.n_q + 5
+    m = np.empty((n_pairs, 2, p.n_ticks, W), dtype=np.float64) if want_metrics else None
+    v = np.empty((n_pairs, 2, p.n_ticks), dtype=np.uint8) if want_metrics else None
+    _chk(lib().cgo_eval_irregular(_ptr(scalars), _ptr(buckets), _ptr(ts_scalars), _ptr(ts_buckets),
+                                  _ptr(cnt_scalars), _ptr(cnt_buckets), _ptr(le), _ptr(has_previous),
+                                  _ptr(start_tick), n_pairs, C.byref(p), _ptr(dec), _ptr(bits), _ptr(m), _ptr(v),
+                                  n_threads), "eval_irregular")
+    return (dec, bits, m, v) if want_metrics else (dec, bits)

@@ -454,6 +454,129 @@ int cgo_eval_lazy(const void* scalars, const void* buckets, const double* le,
     return CG_OK;
 }
 
+/* ---- irregular series: per-series timestamps, ragged lengths --------
+ * Same queries as eval_pv_tick, but every series carries its own time stamps (strictly increasing,
+ * ms) and its own sample count; missed scrapes are simply absent and stale markers have been
+ * dropped by the ingest layer, as Prometheus drops them from range vectors.  Each series selects
+ * its own window (Appendix A "Range selection") and may yield no output (< 2 samples); a bucket
+ * series without output is absent from the `sum(...) by (le)` vector that histogram_quantile sees.
+ *   ts_sc [K][row_pitch] int32, cnt_sc [K];  ts_bk [B][row_pitch] int32, cnt_bk [B]   (one version) */
+static int irregular_increase(const void* vals, int dtype, int64_t row_off, const int32_t* ts, int cnt,
+                              int64_t t, const cg_params* p, double* win, int win_cap, double* inc)
+{
+    const int64_t lo = t - p->window_ms;
+    int a = 0, b = cnt - 1;
+    while (a < cnt && (p->left_open ? (int64_t)ts[a] <= lo : (int64_t)ts[a] < lo)) ++a;
+    while (b >= 0 && (int64_t)ts[b] > t) --b;
+    const int n = b - a + 1;
+    if (n < 2 || n > win_cap) return 0;
+    for (int i = 0; i < n; ++i) win[i] = load_elem(vals, dtype, row_off + a + i);
+    return increase_core(win, n, ts[a], ts[b], t, p->window_ms, inc);
+}
+
+static void eval_pv_tick_irregular(const void* sc, const void* bk, const int32_t* ts_sc, const int32_t* cnt_sc,
+                                   const int32_t* ts_bk, const int32_t* cnt_bk, const double* le,
+                                   const cg_params* p, int tick, double* win, double* m, uint8_t* valid_out)
+{
+    const int nq = p->n_q;
+    const int64_t t = (int64_t)p->tick0_ms + (int64_t)tick * p->tick_step_ms;
+    uint8_t valid = 0;
+    double sums[5] = {0, 0, 0, 0, 0};
+    int have[5] = {0, 0, 0, 0, 0};
+    for (int k = 0; k < p->n_scalar; ++k) {               /* Q2..Q6 (:375, :383, :393, :397, :410) */
+        double inc;
+        if (!irregular_increase(sc, p->dtype, (int64_t)k * p->row_pitch, ts_sc + (int64_t)k * p->row_pitch,
+                                cnt_sc[k], t, p, win, p->row_pitch, &inc)) continue;
+        for (int r = 0; r < 5; ++r)
+            if (p->scalar_role[k] & (1u << r)) { sums[r] = have[r] ? sums[r] + inc : inc; have[r] = 1; }
+    }
+    const double total = sums[0], err = sums[1], lat_sum = sums[2], lat_cnt = sums[3], fb = sums[4];
+    for (int j = 0; j < nq; ++j) m[j] = NAN;
+    {                                                      /* Q1 (:367) over the buckets that have output */
+        double le_p[1024], cnt_p[1024], tmp[1024];
+        int np = 0;
+        const double range_s = (double)p->window_ms / 1000.0;
+        for (int b = 0; b < p->n_buckets; ++b) {
+            double inc;
+            if (!irregular_increase(bk, p->dtype, (int64_t)b * p->row_pitch, ts_bk + (int64_t)b * p->row_pitch,
+                                    cnt_bk[b], t, p, win, p->row_pitch, &inc)) continue;
+            le_p[np] = le[b];
+            cnt_p[np] = inc / range_s;
+            ++np;
+        }
+        if (np > 0) {
+            for (int j = 0; j < nq; ++j) {
+                memcpy(tmp, cnt_p, sizeof(double) * np);
+                m[j] = cgo_bucket_quantile(p->q[j], le_p, tmp, np);
+            }
+            valid |= CG_V_QUANTILE;                         /* non-empty vector (:369-370) */
+        }
+    }
+    m[nq + CG_M_ERROR_RESPONSES] = err;
+    if (total > 0) { m[nq + CG_M_ERROR_RATE] = err / total; valid |= CG_V_ERROR_RATE; }
+    else m[nq + CG_M_ERROR_RATE] = NAN;
+    if (lat_cnt > 0) { m[nq + CG_M_LATENCY_AVG] = lat_sum / lat_cnt; valid |= CG_V_LATENCY_AVG; }
+    else m[nq + CG_M_LATENCY_AVG] = NAN;
+    m[nq + CG_M_REQUEST_COUNT] = lat_cnt;
+    m[nq + CG_M_FEEDBACK_COUNT] = fb;
+    *valid_out = valid;
+}
+
+typedef struct {
+    const void* scalars; const void* buckets;
+    const int32_t* ts_sc; const int32_t* ts_bk; const int32_t* cnt_sc; const int32_t* cnt_bk;
+    const double* le; const uint8_t* has_previous; const int32_t* start_tick; const cg_params* p;
+    cg_decision* decisions; uint32_t* gate_bits; double* metrics; uint8_t* valid;
+} cgo_irr_ctx;
+
+static void irregular_range(int64_t begin, int64_t end, void* ctx)
+{
+    const cgo_irr_ctx* c = (const cgo_irr_ctx*)ctx;
+    const cg_params* p = c->p;
+    const size_t esz = p->dtype == CG_F32 ? 4 : 8;
+    const int nw = (p->n_ticks + 31) / 32, W = cgo_metric_width(p);
+    double* win = (double*)__builtin_alloca(sizeof(double) * (size_t)p->row_pitch);
+    for (int64_t pr = begin; pr < end; ++pr) {
+        uint32_t bits[256];
+        uint32_t* bw = c->gate_bits ? c->gate_bits + pr * nw : bits;
+        memset(bw, 0, sizeof(uint32_t) * nw);
+        for (int j = 0; j < p->n_ticks; ++j) {
+            double m[2][CG_MAX_Q + CG_M_EXTRA];
+            uint8_t v[2];
+            for (int ver = 0; ver < 2; ++ver) {
+                const int64_t pv = pr * 2 + ver;
+                const char* sc = (const char*)c->scalars + (size_t)pv * p->n_scalar * p->row_pitch * esz;
+                const char* bk = c->buckets ? (const char*)c->buckets + (size_t)pv * p->n_buckets * p->row_pitch * esz : 0;
+                eval_pv_tick_irregular(sc, bk, c->ts_sc + (size_t)pv * p->n_scalar * p->row_pitch,
+                                       c->cnt_sc + (size_t)pv * p->n_scalar,
+                                       c->ts_bk ? c->ts_bk + (size_t)pv * p->n_buckets * p->row_pitch : 0,
+                                       c->cnt_bk ? c->cnt_bk + (size_t)pv * p->n_buckets : 0,
+                                       c->le, p, j, win, m[ver], &v[ver]);
+                if (c->metrics) memcpy(c->metrics + ((size_t)pv * p->n_ticks + j) * W, m[ver], sizeof(double) * W);
+                if (c->valid) c->valid[(size_t)pv * p->n_ticks + j] = v[ver];
+            }
+            if (gate_one(m[0], v[0], m[1], v[1], p) & CG_G_PROMOTE) bw[j >> 5] |= 1u << (j & 31);
+        }
+        if (c->decisions)
+            replay_one(bw, c->has_previous ? c->has_previous[pr] : 1,
+                       c->start_tick ? c->start_tick[pr] : p->start_tick, p, c->decisions + pr);
+    }
+}
+
+int cgo_eval_irregular(const void* scalars, const void* buckets, const int32_t* ts_scalars,
+                       const int32_t* ts_buckets, const int32_t* cnt_scalars, const int32_t* cnt_buckets,
+                       const double* le, const uint8_t* has_previous, const int32_t* start_tick,
+                       int64_t n_pairs, const cg_params* p, cg_decision* decisions, uint32_t* gate_bits,
+                       double* metrics, uint8_t* valid, int n_threads)
+{
+    if (p->n_buckets > 1024 || p->n_q > CG_MAX_Q || p->n_ticks < 0) return CG_EINVAL;
+    if (!gate_bits && (p->n_ticks + 31) / 32 > 256) return CG_EINVAL;
+    cgo_irr_ctx c = {scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le,
+                     has_previous, start_tick, p, decisions, gate_bits, metrics, valid};
+    parallel_for(n_pairs, n_threads, irregular_range, &c);
+    return CG_OK;
+}
+
 int cgo_max_threads(void)
 {
     long n = sysconf(_SC_NPROCESSORS_ONLN);

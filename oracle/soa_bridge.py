@@ -35,11 +35,18 @@ def pair_to_db(batch, pair: int, name: str = "m", namespace: str = "ns",
     for ver in range(2):
         base = {"deployment_name": name, "predictor_name": f"v{versions[ver]}",
                 "namespace": namespace}
-        ts = [int(batch.phase[pair, ver]) + i * p.period_ms for i in range(T)]
+        irregular = hasattr(batch, "ts_scalars")      # synth.IrregularBatch: per-series time stamps and counts
+        ts = None if irregular else [int(batch.phase[pair, ver]) + i * p.period_ms for i in range(T)]
+
+        def series(values, ts_arr, cnt_arr, r):
+            if not irregular:
+                return list(zip(ts, [float(x) for x in values[pair, ver, r, :T]]))
+            n = int(cnt_arr[pair, ver, r])
+            return list(zip([int(x) for x in ts_arr[pair, ver, r, :n]], [float(x) for x in values[pair, ver, r, :n]]))
+
         for k in range(p.n_scalar):
             role = p.scalar_role[k]
-            vals = [float(x) for x in batch.scalars[pair, ver, k, :T]]
-            samples = list(zip(ts, vals))
+            samples = series(batch.scalars, getattr(batch, "ts_scalars", None), getattr(batch, "cnt_scalars", None), k)
             if role & _R_TOTAL:
                 labels = dict(base, series=str(k), service="predictions",
                               code="500" if role & _R_ERR else "200")
@@ -53,9 +60,8 @@ def pair_to_db(batch, pair: int, name: str = "m", namespace: str = "ns",
             else:
                 raise ValueError(f"scalar series {k} has no role the reference queries")
         for b in range(p.n_buckets):
-            vals = [float(x) for x in batch.buckets[pair, ver, b, :T]]
             db.add(CLIENT_BUCKET, dict(base, le=_le_label(float(batch.le[b]))),
-                   list(zip(ts, vals)))
+                   series(batch.buckets, getattr(batch, "ts_buckets", None), getattr(batch, "cnt_buckets", None), b))
     return db
 
 

@@ -36,6 +36,7 @@ def _load():
     lib.cg_synth_fill.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _vp, C.c_uint64, C.c_double, C.c_double, _vp]
     lib.cg_eval_fused_path.argtypes = [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp]
     lib.cg_stream_eligible.argtypes = [_vp]
+    lib.cg_eval_irregular.argtypes = [_vp] * 9 + [_i64] + [_vp] * 6
     lib.cg_launch_info.argtypes = [_vp, _i64, _vp, _vp, _vp]
     for name in OPTIONAL:
         pass

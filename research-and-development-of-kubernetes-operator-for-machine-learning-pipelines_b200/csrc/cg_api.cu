@@ -11,6 +11,7 @@
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
 #include "cg_stream.cuh"
+#include "cg_irregular.cuh"
 #include "cg_synth.cuh"
 
 namespace {
@@ -297,6 +298,64 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     return p->dtype == CG_F32 ? launch_general<float>(plan, s) : launch_general<double>(plan, s);
 }
 
+
+// ---- irregular series: shared-memory plan and launch -----------------------------------
+struct IrregularPlan {
+    cg::IrregularArgs args;
+    int grid, block;
+};
+
+int plan_irregular(const cg_params* p, int64_t n_pairs, IrregularPlan* plan) {
+    cg::IrregularArgs& a = plan->args;
+    memset(&a, 0, sizeof(a));
+    a.p = *p;
+    a.n_pairs = n_pairs;
+    const size_t esz = elem_size(p);
+    const size_t rows = (size_t)p->n_scalar + p->n_buckets;
+    if (p->row_pitch % 4) return fail(CG_EINVAL, "irregular series: row_pitch must be a multiple of 4 samples");
+    size_t off = rows * p->row_pitch * esz;
+    off = (off + 15) & ~(size_t)15;
+    a.off_ts = (uint32_t)off;           off += rows * p->row_pitch * 4;
+    a.off_cnt = (uint32_t)off;          off += rows * 12;     // counts, first time stamps, search hints
+    off = (off + 7) & ~(size_t)7;
+    a.off_le = (uint32_t)off;           off += (size_t)p->n_buckets * 8;
+    a.off_stash = (uint32_t)off;        off += (size_t)p->n_ticks * 3 * 8;
+    a.off_stash_valid = (uint32_t)off;  off += ((size_t)p->n_ticks + 7) & ~(size_t)7;
+    a.off_bits = (uint32_t)off;         off += (((size_t)p->n_ticks + 31) / 32) * 4;
+    off = (off + 7) & ~(size_t)7;
+    a.off_bar = (uint32_t)off;          off += 8;
+    if (off > (size_t)kMaxSmem)
+        return fail(CG_EINVAL, "irregular series: values + time stamps of one (pair, version) need %zu bytes of shared "
+                    "memory (limit %d): (n_scalar+n_buckets)*row_pitch too large", off, kMaxSmem);
+    if (rows * p->row_pitch * (esz + 4) >= (1u << 20))
+        return fail(CG_EINVAL, "tile exceeds the mbarrier transaction-count range");
+    a.smem_bytes = (uint32_t)off;
+    int threads = ((p->n_ticks + 31) / 32) * 32;
+    if (threads < 32) threads = 32;
+    if (threads > 512) threads = 512;
+    plan->block = threads;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per_sm = (int)(kMaxSmem / (off + 1024)) > 0 ? (int)(kMaxSmem / (off + 1024)) : 1;
+    int64_t g = (int64_t)sms * per_sm;
+    if (g > n_pairs) g = n_pairs;
+    if (g < 1) g = 1;
+    plan->grid = (int)g;
+    return CG_OK;
+}
+
+template <typename T>
+int launch_irregular(const IrregularPlan& plan, cudaStream_t s) {
+    auto kern = cg::irregular_kernel<T>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.args.smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(irregular_kernel)");
+    kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch irregular_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -363,6 +422,37 @@ int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const
     if (path < 0 || path > 2) return fail(CG_EINVAL, "path must be 0 (auto), 1 (general) or 2 (streaming)");
     return run_general(scalars, buckets, le, phase, has_previous, start_tick, n_pairs, p, decisions,
                        gate_bits, metrics, valid, stream, path);
+}
+
+int cg_eval_irregular(const void* scalars, const void* buckets, const int32_t* ts_scalars,
+                      const int32_t* ts_buckets, const int32_t* cnt_scalars, const int32_t* cnt_buckets,
+                      const double* le, const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
+                      const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
+                      uint8_t* valid, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (n_pairs == 0) return CG_OK;
+    if (!decisions && !gate_bits && !metrics && !valid) return fail(CG_EINVAL, "no output requested");
+    if (p->n_scalar > 0 && (!scalars || !ts_scalars || !cnt_scalars))
+        return fail(CG_EINVAL, "scalars / ts_scalars / cnt_scalars is NULL but n_scalar > 0");
+    if (p->n_buckets > 0 && (!buckets || !ts_buckets || !cnt_buckets || !le))
+        return fail(CG_EINVAL, "buckets / ts_buckets / cnt_buckets / le is NULL but n_buckets > 0");
+    if ((rc = check_aligned(scalars, "scalars")) || (rc = check_aligned(buckets, "buckets")) ||
+        (rc = check_aligned(ts_scalars, "ts_scalars")) || (rc = check_aligned(ts_buckets, "ts_buckets")))
+        return rc;
+    if ((int64_t)p->tick0_ms + (int64_t)p->n_ticks * p->tick_step_ms >= (1ll << 31) ||
+        (int64_t)p->tick0_ms - p->window_ms <= -(1ll << 31))
+        return fail(CG_EINVAL, "irregular series: tick times must fit int32 milliseconds");
+    IrregularPlan plan;
+    if ((rc = plan_irregular(p, n_pairs, &plan))) return rc;
+    cg::IrregularArgs& a = plan.args;
+    a.scalars = scalars; a.buckets = buckets; a.ts_scalars = ts_scalars; a.ts_buckets = ts_buckets;
+    a.cnt_scalars = cnt_scalars; a.cnt_buckets = cnt_buckets; a.le = le;
+    a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
+    a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
+    return p->dtype == CG_F32 ? launch_irregular<float>(plan, (cudaStream_t)stream)
+                              : launch_irregular<double>(plan, (cudaStream_t)stream);
 }
 
 int cg_stream_eligible(const cg_params* p) {

@@ -130,6 +130,51 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
     return res[0] if len(res) == 1 else tuple(res)
 
 
+def eval_irregular(scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, p: CgParams,
+                   has_previous=None, start_tick=None, want_bits: bool = False, want_metrics: bool = False):
+    """The fused step for irregular series: every series has its own int32 ms
+    time stamps `ts_*[N, 2, K|B, pitch]` and sample count `cnt_*[N, 2, K|B]`; stale markers already
+    dropped (ingest.build_irregular_batch does it).  -> decisions [N, 6] (+ gate_bits, metrics, valid)."""
+    n = int(cnt_scalars.shape[0])
+    dev = cnt_scalars.device
+    if dev.type != "cuda":
+        raise ValueError("series must live on the GPU; there is no CPU fallback")
+    vdt = torch.float32 if p.dtype == 1 else torch.float64
+    for t, dt, shape, what in ((scalars, vdt, (n, 2, p.n_scalar, p.row_pitch), "scalars"),
+                               (ts_scalars, torch.int32, (n, 2, p.n_scalar, p.row_pitch), "ts_scalars"),
+                               (cnt_scalars, torch.int32, (n, 2, p.n_scalar), "cnt_scalars")) + \
+            (((buckets, vdt, (n, 2, p.n_buckets, p.row_pitch), "buckets"),
+              (ts_buckets, torch.int32, (n, 2, p.n_buckets, p.row_pitch), "ts_buckets"),
+              (cnt_buckets, torch.int32, (n, 2, p.n_buckets), "cnt_buckets")) if p.n_buckets else ()):
+        _want(t, dt, what)
+        if tuple(t.shape) != shape:
+            raise ValueError(f"{what}: shape {tuple(t.shape)}, expected {shape}")
+    if p.n_buckets:
+        _want(le, torch.float64, "le")
+    if has_previous is not None:
+        _want(has_previous, torch.uint8, "has_previous")
+    if start_tick is not None:
+        _want(start_tick, torch.int32, "start_tick")
+    dec = torch.empty((n, 6), dtype=torch.int32, device=dev)
+    bits = torch.empty((n, p.n_words), dtype=torch.int32, device=dev) if want_bits else None
+    metrics = valid = None
+    if want_metrics:
+        metrics = torch.empty((n, 2, p.n_ticks, p.metric_width), dtype=torch.float64, device=dev)
+        valid = torch.empty((n, 2, p.n_ticks), dtype=torch.uint8, device=dev)
+    nb = bool(p.n_buckets)
+    _lib.check(_lib.lib.cg_eval_irregular(_ptr(scalars), _ptr(buckets if nb else None), _ptr(ts_scalars),
+                                          _ptr(ts_buckets if nb else None), _ptr(cnt_scalars),
+                                          _ptr(cnt_buckets if nb else None), _ptr(le if nb else None),
+                                          _ptr(has_previous), _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits),
+                                          _ptr(metrics), _ptr(valid), _stream_ptr()), "cg_eval_irregular")
+    res = [dec]
+    if want_bits:
+        res.append(bits)
+    if want_metrics:
+        res += [metrics, valid]
+    return res[0] if len(res) == 1 else tuple(res)
+
+
 def stream_eligible(p: CgParams) -> bool:
     """True if cg_eval_fused takes the streaming kernel for these params."""
     return bool(_lib.lib.cg_stream_eligible(C.byref(p)))

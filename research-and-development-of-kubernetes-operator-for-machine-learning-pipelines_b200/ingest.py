@@ -13,8 +13,10 @@ Label rules are the reference's matchers:
   seldon_api_executor_client_requests_seconds_bucket  one series per `le`            (:367)
 all selected by (deployment_name, predictor_name, namespace).
 
-Only regular scrape grids are accepted here (sample i at phase + i*period); irregular series
-and stale markers are the next row of SURVEY.md 8(f) and raise `IrregularSeries`.
+`build_host_batch` accepts regular scrape grids only (sample i at phase + i*period) and raises
+`IrregularSeries` otherwise; `build_irregular_batch` takes any series: it keeps
+each series' own time stamps, drops stale markers the way Prometheus drops them from range vectors,
+and leaves absent series as rows with zero samples.  The device side of that is cg_eval_irregular.
 """
 from __future__ import annotations
 
@@ -186,3 +188,105 @@ def to_store(host: HostSeries, device="cuda", now_ms: Optional[int] = None):
     """Upload an ingested batch to the GPU as an operator_api.SeriesStore."""
     from .operator_api import SeriesStore
     return SeriesStore.from_host(host, device=device, index=host.index, now_ms=now_ms)
+
+
+# ---- irregular series (SURVEY.md 8(f) row 2) ---------------------------------------------
+STALE_NAN_BITS = 0x7FF0000000000002          # Prometheus value.StaleNaN: "this series ended here"
+
+
+def drop_stale(ts: np.ndarray, values: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """Remove stale markers from one series (raw TSDB / remote-read samples carry them; the JSON
+    query API never shows them).  They are not samples: range vectors skip them."""
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    keep = v.view(np.uint64) != np.uint64(STALE_NAN_BITS)
+    return np.asarray(ts)[keep], v[keep]
+
+
+class HostIrregular:
+    """What `build_irregular_batch` returns: values, per-series int32 ms time stamps (relative to
+    epoch_ms) and sample counts, in the layout cg_eval_irregular reads, plus the label index."""
+
+    def __init__(self, scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, params, index, epoch_ms):
+        self.scalars, self.buckets, self.ts_scalars, self.ts_buckets = scalars, buckets, ts_scalars, ts_buckets
+        self.cnt_scalars, self.cnt_buckets, self.le = cnt_scalars, cnt_buckets, le
+        self.params, self.index, self.epoch_ms = params, index, epoch_ms
+
+
+def build_irregular_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str, str], Tuple[str, str]],
+                          epoch_ms: Optional[int] = None, dtype: int = 0, **param_overrides) -> HostIrregular:
+    """Like build_host_batch, for series that are not on a grid.  The scalar rows are the union of
+    the label sets seen (a (pair, version) that lacks one gets a row with zero samples), the bucket
+    rows the union of the `le` values; samples keep their own time stamps; stale markers are dropped;
+    time stamps must be strictly increasing within a series and fit int32 ms from epoch_ms."""
+    pairs = sorted(versions)
+    if not pairs:
+        raise ValueError("no model pairs")
+    row_of = {key: i for i, key in enumerate(pairs)}
+    ver_of = {}
+    for key, (new, old) in versions.items():
+        ver_of[(key, new)] = 0
+        ver_of[(key, old)] = 1
+    scal: Dict[tuple, Dict[Tuple[int, int], Tuple[np.ndarray, np.ndarray]]] = {}
+    buck: Dict[float, Dict[Tuple[int, int], Tuple[np.ndarray, np.ndarray]]] = {}
+    roles: Dict[tuple, int] = {}
+    for name, answer in answers.items():
+        for labels, ts, v in parse_matrix(answer):
+            key = (labels.get("deployment_name", ""), labels.get("namespace", ""))
+            vk = ver_of.get((key, labels.get("predictor_name", "")))
+            if vk is None:
+                continue
+            ts, v = drop_stale(ts, v)
+            if len(ts) > 1 and not np.all(np.diff(ts) > 0):
+                raise ValueError(f"{name}{labels}: time stamps are not strictly increasing")
+            slot = (row_of[key], vk)
+            if name == CLIENT_BUCKET:
+                buck.setdefault(_le_value(labels["le"]), {})[slot] = (ts, v)
+            else:
+                order = ((SERVER_COUNT, CLIENT_SUM, CLIENT_COUNT).index(name), name,
+                         tuple(sorted((k, x) for k, x in labels.items()
+                                      if k not in ("deployment_name", "namespace", "predictor_name"))))
+                roles[order] = _scalar_role(name, labels)
+                scal.setdefault(order, {})[slot] = (ts, v)
+    series = [s for d in list(scal.values()) + list(buck.values()) for s in d.values()]
+    if not series:
+        raise ValueError("no series matched")
+    firsts = [int(ts[0]) for ts, _ in series if len(ts)]
+    if epoch_ms is None:
+        epoch_ms = min(firsts) if firsts else 0
+    T = max(4, max(len(ts) for ts, _ in series))
+    dt = np.float32 if dtype == 1 else np.float64
+    pitch = -(-T // 4) * 4                                   # multiple of 4 samples: 16-byte rows in both arrays
+    n, orders, les = len(pairs), sorted(scal), sorted(buck)
+    K, B = len(orders), len(les)
+
+    def fill(groups, R):
+        vals = np.zeros((n, 2, R, pitch), dtype=dt)
+        tss = np.zeros((n, 2, R, pitch), dtype=np.int32)
+        cnt = np.zeros((n, 2, R), dtype=np.int32)
+        for r, g in enumerate(groups):
+            for (i, vk), (ts, v) in g.items():
+                rel = np.asarray(ts, dtype=np.int64) - epoch_ms
+                if len(rel) and (rel.min() < -(1 << 31) or rel.max() >= (1 << 31)):
+                    raise ValueError("time stamps do not fit int32 milliseconds from epoch_ms")
+                m = len(rel)
+                vals[i, vk, r, :m], tss[i, vk, r, :m], cnt[i, vk, r] = v, rel, m
+        return vals, tss, cnt
+
+    scalars, ts_s, cnt_s = fill([scal[o] for o in orders], K)
+    buckets, ts_b, cnt_b = fill([buck[x] for x in les], B)
+    params = make_params(n_samples=T, row_pitch=pitch, n_scalar=K, n_buckets=B, roles=[roles[o] for o in orders],
+                         dtype=dtype, **param_overrides)
+    index = {key: (row_of[key], {versions[key][0]: 0, versions[key][1]: 1}) for key in pairs}
+    return HostIrregular(scalars, buckets, ts_s, ts_b, cnt_s, cnt_b, np.array(les, dtype=np.float64), params,
+                         index, epoch_ms)
+
+
+def evaluate_irregular(host: HostIrregular, device="cuda", has_previous=None, start_tick=None, want_bits: bool = False):
+    """Upload an irregular batch and run the whole canary on it (engine.eval_irregular)."""
+    import torch
+
+    from . import engine
+    up = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(device)   # noqa: E731
+    return engine.eval_irregular(up(host.scalars), up(host.buckets), up(host.ts_scalars), up(host.ts_buckets),
+                                 up(host.cnt_scalars), up(host.cnt_buckets), up(host.le), host.params,
+                                 has_previous=up(has_previous), start_tick=up(start_tick), want_bits=want_bits)

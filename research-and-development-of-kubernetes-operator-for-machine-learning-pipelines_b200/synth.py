@@ -152,3 +152,77 @@ def generate(p: CgParams, n_pairs: int, seed: int = 0xC0FFEE, resets: bool = Tru
         ph[:, 1] = ph[:, 0]
     return SynthBatch(scalars=scalars, buckets=buckets, le=le,
                       phase=ph.astype(np.int32), params=p)
+
+
+@dataclass
+class IrregularBatch:
+    """Series with their own time stamps.  Only the first cnt samples of a
+    row are meaningful; the rest is padding."""
+    scalars: np.ndarray      # [N, 2, K, pitch]
+    buckets: np.ndarray      # [N, 2, B, pitch]
+    ts_scalars: np.ndarray   # [N, 2, K, pitch] int32 ms, strictly increasing within a row
+    ts_buckets: np.ndarray   # [N, 2, B, pitch]
+    cnt_scalars: np.ndarray  # [N, 2, K] int32
+    cnt_buckets: np.ndarray  # [N, 2, B] int32
+    le: np.ndarray           # [B]
+    params: CgParams
+
+
+def as_irregular(batch: SynthBatch) -> IrregularBatch:
+    """The same grid series, spelled with explicit time stamps (results must not change)."""
+    p = batch.params
+    N, pitch, T = batch.phase.shape[0], p.row_pitch, p.n_samples
+    grid = batch.phase[:, :, None, None].astype(np.int64) + np.arange(pitch, dtype=np.int64) * p.period_ms
+    ts_s = np.broadcast_to(grid, (N, 2, p.n_scalar, pitch)).astype(np.int32)
+    ts_b = np.broadcast_to(grid, (N, 2, p.n_buckets, pitch)).astype(np.int32)
+    return IrregularBatch(scalars=batch.scalars, buckets=batch.buckets,
+                          ts_scalars=np.ascontiguousarray(ts_s), ts_buckets=np.ascontiguousarray(ts_b),
+                          cnt_scalars=np.full((N, 2, p.n_scalar), T, np.int32),
+                          cnt_buckets=np.full((N, 2, p.n_buckets), T, np.int32), le=batch.le, params=p)
+
+
+def make_irregular(batch: SynthBatch, seed: int = 1, jitter_ms: int = 2000, miss_prob: float = 0.05,
+                   series_miss_prob: float = 0.01, gap_prob: float = 0.02, truncate_prob: float = 0.05,
+                   dead_series_prob: float = 0.01) -> IrregularBatch:
+    """Perturb a grid batch the way real scrapes deviate from a grid:
+      * every scrape of a target is late or early by up to jitter_ms (all its series alike);
+      * scrapes fail (miss_prob: the whole target; series_miss_prob: one series);
+      * targets go away for a few scrapes (gap_prob starts a gap of 2..6 scrapes: windows with 2-3
+        samples, and the avg*1.1 extrapolation threshold of Appendix A step 5 is crossed);
+      * series start late or end early (truncate_prob) or have no samples at all (dead_series_prob)."""
+    p = batch.params
+    rng = np.random.default_rng(seed)
+    N, T, pitch, K, B = batch.phase.shape[0], p.n_samples, p.row_pitch, p.n_scalar, p.n_buckets
+    out = as_irregular(batch)
+    vals = [np.zeros_like(batch.scalars), np.zeros_like(batch.buckets)]
+    tss = [np.zeros_like(out.ts_scalars), np.zeros_like(out.ts_buckets)]
+    cnts = [np.zeros_like(out.cnt_scalars), np.zeros_like(out.cnt_buckets)]
+    half = max(1, min(jitter_ms, p.period_ms // 2 - 1))
+    for i in range(N):
+        for v in range(2):
+            t_grid = int(batch.phase[i, v]) + np.arange(T, dtype=np.int64) * p.period_ms
+            t_tgt = t_grid + rng.integers(-half, half + 1, size=T)
+            keep_tgt = rng.random(T) >= miss_prob
+            j = 0
+            while j < T:
+                if rng.random() < gap_prob:
+                    g = int(rng.integers(2, 7))
+                    keep_tgt[j:j + g] = False
+                    j += g
+                j += 1
+            for which, (src, R) in enumerate(((batch.scalars, K), (batch.buckets, B))):
+                for r in range(R):
+                    keep = keep_tgt & (rng.random(T) >= series_miss_prob)
+                    if rng.random() < truncate_prob:
+                        a, b = sorted(rng.integers(0, T + 1, size=2))
+                        keep[:a] = False
+                        keep[b:] = False
+                    if rng.random() < dead_series_prob:
+                        keep[:] = False
+                    idx = np.nonzero(keep)[0]
+                    n = len(idx)
+                    vals[which][i, v, r, :n] = src[i, v, r, idx]
+                    tss[which][i, v, r, :n] = t_tgt[idx]
+                    cnts[which][i, v, r] = n
+    return IrregularBatch(scalars=vals[0], buckets=vals[1], ts_scalars=tss[0], ts_buckets=tss[1],
+                          cnt_scalars=cnts[0], cnt_buckets=cnts[1], le=batch.le, params=p)

@@ -13,6 +13,10 @@ Run in the BUILD container (needs /root/reference):  python tests/golden/make_go
                          unmodified reference run on oracle/pyoracle.py's fake Prometheus:
                          per-tick get_model_metrics dicts (:363-417) on a tick subsample,
                          the final weights / state / evaluation count of the canary loop
+  ref_irregular_cases.npz/.json  the same for IRREGULAR series (jittered and
+                         missed scrapes, gaps, series that start late, end early or are absent)
+
+`python tests/golden/make_golden.py irregular` regenerates only the last pair of files.
 """
 import json
 import math
@@ -196,11 +200,56 @@ def canary_cases():
                        "unmodified over oracle/pyoracle.py FakePrometheus", cases=cases)
 
 
+def irregular_cases():
+    cases = []
+    arrays = {}
+    geoms = [
+        ("irr", dict(n_samples=120, n_scalar=4, n_buckets=8), 6, 0xC0FFEE + 200, 0.3,
+         dict(seed=7, miss_prob=0.08, gap_prob=0.03, truncate_prob=0.1, dead_series_prob=0.03)),
+        ("irr_open", dict(n_samples=80, n_scalar=4, n_buckets=6, left_open=True), 3, 0xC0FFEE + 201, 0.0,
+         dict(seed=8, jitter_ms=0, miss_prob=0.1, gap_prob=0.05)),     # no jitter: samples on window edges
+    ]
+    for gname, kw, n_pairs, seed, adv, irr in geoms:
+        p = P.make_params(**kw)
+        lo = bool(kw.get("left_open"))
+        grid = synth.generate(p, n_pairs, seed=seed, adversarial=adv, coincident_phase=lo)
+        batch = synth.make_irregular(grid, **irr)
+        for field in ("scalars", "buckets", "ts_scalars", "ts_buckets", "cnt_scalars", "cnt_buckets", "le"):
+            arrays[f"{gname}_{field}"] = getattr(batch, field)
+        for pair in range(n_pairs):
+            db = sb.pair_to_db(batch, pair, left_open=lo)
+            ticks = sorted(set(list(range(0, p.n_ticks, 7)) + [0, 1, 2, p.n_ticks - 1]))
+            per_tick = []
+            for j in ticks:
+                fp = rl.FakePrometheus(db, rl.VirtualClock(p.tick0_ms + j * p.tick_step_ms))
+                rec = {"tick": j}
+                mds = []
+                for ver, pred in enumerate(("v2", "v1")):
+                    md = rl.reference_get_model_metrics(fp, "m", pred, "ns")
+                    mds.append(md)
+                    rec["new" if ver == 0 else "old"] = {k: fenc(v) for k, v in md.items()}
+                rec["promote"] = bool(rl.reference_should_promote(mds[0], mds[1], dict(P.REFERENCE_THRESHOLDS)))
+                per_tick.append(rec)
+            runs = []
+            for start in (0, 4):
+                r = sb.run_reference_on_pair(batch, pair, start_tick=start, left_open=lo)
+                runs.append(dict(start_tick=start, cur=r["cur"], prev=r["prev"], state=r["state"],
+                                 n_promotions=r["n_promotions"], n_evals=r["n_evals"],
+                                 weights=r["weights"], end_ms=r["end_ms"], events=r["events"]))
+            cases.append(dict(geometry=gname, make_params=kw, pair=pair, ticks=per_tick, runs=runs))
+    np.savez_compressed(os.path.join(HERE, "ref_irregular_cases.npz"), **arrays)
+    return dict(source="mlflow_operator.py get_model_metrics/should_promote_model/step loop run unmodified over "
+                       "oracle/pyoracle.py FakePrometheus; series with per-series time stamps", cases=cases)
+
+
 def main():
     assert rl.reference_available(), "needs /root/reference"
-    for name, fn in (("kat_promql.json", kat), ("ref_gate_probes.json", gate_probes),
-                     ("ref_schedule_probes.json", schedule_probes),
-                     ("ref_canary_cases.json", canary_cases)):
+    todo = (("kat_promql.json", kat), ("ref_gate_probes.json", gate_probes),
+            ("ref_schedule_probes.json", schedule_probes), ("ref_canary_cases.json", canary_cases),
+            ("ref_irregular_cases.json", irregular_cases))
+    if sys.argv[1:] == ["irregular"]:
+        todo = todo[-1:]
+    for name, fn in todo:
         with open(os.path.join(HERE, name), "w") as f:
             json.dump(fn(), f, indent=1)
         print("wrote", name)

@@ -56,6 +56,22 @@ def load_canary_batches():
     return batches, doc["cases"]
 
 
+def load_irregular_batches():
+    """-> {geometry: synth.IrregularBatch}, list of cases (tests/golden/ref_irregular_cases.*)."""
+    import canary_b200  # noqa: F401
+    from canary_b200 import params as P, synth
+    arrays = np.load(os.path.join(GOLDEN, "ref_irregular_cases.npz"))
+    doc = load_json("ref_irregular_cases.json")
+    batches = {}
+    for case in doc["cases"]:
+        g = case["geometry"]
+        if g not in batches:
+            fields = {f: np.ascontiguousarray(arrays[f"{g}_{f}"]) for f in
+                      ("scalars", "buckets", "ts_scalars", "ts_buckets", "cnt_scalars", "cnt_buckets", "le")}
+            batches[g] = synth.IrregularBatch(params=P.make_params(**case["make_params"]), **fields)
+    return batches, doc["cases"]
+
+
 def golden_record(md, n_q=1):
     """Golden metrics dict (hex floats / None) -> (record[n_q+5], valid)."""
     rec = np.full(n_q + 5, np.nan)

@@ -70,5 +70,68 @@ def test_special_values_and_errors():
     doc = json.loads(wire[ingest.CLIENT_COUNT])
     doc["data"]["result"][0]["values"][3][0] += 1.0          # one late scrape
     wire[ingest.CLIENT_COUNT] = json.dumps(doc)
-    with pytest.raises(ingest.IrregularSeries):
+    with pytest.raises(ValueError):          # the grid ingest refuses (IrregularSeries, or a series is missing)
         ingest.build_host_batch(wire, versions, period_ms=p.period_ms, epoch_ms=epoch)
+
+
+# ---- irregular series ---------------------------------------------
+def render_irregular(ib, epoch_ms=1_700_000_000_000):
+    p = ib.params
+    answers = {ingest.SERVER_COUNT: [], ingest.CLIENT_SUM: [], ingest.CLIENT_COUNT: [], ingest.CLIENT_BUCKET: []}
+    versions = {}
+    for i in range(ib.cnt_scalars.shape[0]):
+        key = (f"model-{i:03d}", "prod")
+        versions[key] = ("v2", "v1")
+        for v, pred in enumerate(("v2", "v1")):
+            base = {"deployment_name": key[0], "namespace": key[1], "predictor_name": pred}
+
+            def series(labels, vals, ts, n):
+                return {"metric": labels, "values": [[(epoch_ms + int(t)) / 1000.0, repr(float(x))]
+                                                      for t, x in zip(ts[:n], vals[:n])]}
+            rows = [(ingest.SERVER_COUNT, dict(base, code="200", service="predictions")),
+                    (ingest.SERVER_COUNT, dict(base, code="500", service="predictions")),
+                    (ingest.CLIENT_SUM, dict(base)), (ingest.CLIENT_COUNT, dict(base))]
+            for k, (name, labels) in enumerate(rows):
+                n = int(ib.cnt_scalars[i, v, k])
+                if n:       # Prometheus does not return a series without samples in the range
+                    answers[name].append(series(labels, ib.scalars[i, v, k], ib.ts_scalars[i, v, k], n))
+            for b in range(p.n_buckets):
+                n = int(ib.cnt_buckets[i, v, b])
+                le = "+Inf" if math.isinf(ib.le[b]) else repr(float(ib.le[b]))
+                if n:
+                    answers[ingest.CLIENT_BUCKET].append(series(dict(base, le=le), ib.buckets[i, v, b], ib.ts_buckets[i, v, b], n))
+    wire = {name: json.dumps({"status": "success", "data": {"resultType": "matrix", "result": res}})
+            for name, res in answers.items()}
+    return wire, versions, epoch_ms
+
+
+def test_irregular_round_trip_and_decisions():
+    p = P.make_params(n_samples=96, n_buckets=10)
+    ib = synth.make_irregular(synth.generate(p, 6, seed=5, adversarial=0.3), seed=2, miss_prob=0.1, gap_prob=0.05,
+                              dead_series_prob=0.05)
+    wire, versions, epoch = render_irregular(ib)
+    with pytest.raises(ValueError):          # the grid ingest refuses (IrregularSeries, or a series is missing)
+        ingest.build_host_batch(wire, versions, period_ms=p.period_ms, epoch_ms=epoch)
+    host = ingest.build_irregular_batch(wire, versions, epoch_ms=epoch)
+    hp = host.params
+    assert hp.n_scalar == 4 and hp.n_buckets == 10 and hp.row_pitch % 4 == 0
+    assert tuple(hp.scalar_role[:4]) == tuple(p.scalar_role[:4]) and np.array_equal(host.le, ib.le)
+    assert np.array_equal(host.cnt_scalars, ib.cnt_scalars) and np.array_equal(host.cnt_buckets, ib.cnt_buckets)
+    for got_v, got_t, cnt, want_v, want_t in ((host.scalars, host.ts_scalars, ib.cnt_scalars, ib.scalars, ib.ts_scalars),
+                                              (host.buckets, host.ts_buckets, ib.cnt_buckets, ib.buckets, ib.ts_buckets)):
+        for idx in np.ndindex(cnt.shape):
+            n = cnt[idx]
+            assert np.array_equal(got_v[idx][:n], want_v[idx][:n]) and np.array_equal(got_t[idx][:n], want_t[idx][:n])
+    want = co.eval_irregular(ib.scalars, ib.buckets, ib.ts_scalars, ib.ts_buckets, ib.cnt_scalars, ib.cnt_buckets,
+                             ib.le, p)[0]
+    got = co.eval_irregular(host.scalars, host.buckets, host.ts_scalars, host.ts_buckets, host.cnt_scalars,
+                            host.cnt_buckets, host.le, hp)[0]
+    assert np.array_equal(got, want)
+
+
+def test_stale_markers_are_not_samples():
+    stale = np.array([ingest.STALE_NAN_BITS], dtype=np.uint64).view(np.float64)[0]
+    ts = np.array([0, 15000, 30000, 45000, 60000])
+    v = np.array([1.0, 2.0, stale, float("nan"), 5.0])
+    t2, v2 = ingest.drop_stale(ts, v)
+    assert list(t2) == [0, 15000, 45000, 60000] and math.isnan(v2[2]) and v2[3] == 5.0   # an ordinary NaN stays
