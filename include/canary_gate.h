@@ -82,6 +82,12 @@ extern "C" {
 #define CG_STATE_COMPLETE    1 /* reached max_traffic; old predictor dropped (:355-361) */
 #define CG_STATE_ABORTED     2 /* max_attempts consecutive failures; weights frozen (:341-349) */
 #define CG_STATE_NO_CANARY   3 /* no previous version: 100/0, no loop (:188-191, :289) */
+#define CG_STATE_ROLLED_BACK 4 /* only with on_abort = CG_ABORT_ROLLBACK: as ABORTED, then all traffic back to the old version */
+
+/* what the schedule does after max_attempts consecutive failures */
+#define CG_ABORT_FREEZE   0    /* the reference: log, event, weights stay where they are (:341-349) */
+#define CG_ABORT_ROLLBACK 1    /* opt-in extension (the reference leaves a placeholder at :345):
+                                * traffic_current = 0, traffic_prev = max_traffic */
 
 typedef struct cg_params {
     int32_t struct_bytes;        /* = sizeof(cg_params); checked by every entry point */
@@ -115,6 +121,7 @@ typedef struct cg_params {
     int32_t attempt_delay_ticks; /* attempt_delay / tick_step = 1 (:294) */
     int32_t start_tick;          /* tick at which the canary loop starts (:296) */
     int32_t reserved;
+    int32_t on_abort;            /* CG_ABORT_FREEZE (reference, default) | CG_ABORT_ROLLBACK */
 } cg_params;
 
 /* Decision record, 24 bytes. */

@@ -283,6 +283,9 @@ static void replay_one(const uint32_t* bits, int has_previous, int start_tick,
         tick += p->interval_ticks;                          /* :352 */
     }
     if (cur == p->max_traffic) state = CG_STATE_COMPLETE;   /* :355 */
+    if (state == CG_STATE_ABORTED && p->on_abort == CG_ABORT_ROLLBACK) {   /* opt-in; the reference has a placeholder at :345 */
+        cur = 0; prev = p->max_traffic; state = CG_STATE_ROLLED_BACK;
+    }
     out->traffic_current = cur; out->traffic_prev = prev; out->state = state;
     out->n_promotions = n_prom; out->n_evals = n_eval; out->last_tick = last;
 }
@@ -438,6 +441,9 @@ static void lazy_range(int64_t begin, int64_t end, void* ctx)
             tick += p->interval_ticks;
         }
         if (cur == p->max_traffic) state = CG_STATE_COMPLETE;
+        if (state == CG_STATE_ABORTED && p->on_abort == CG_ABORT_ROLLBACK) {
+            cur = 0; prev = p->max_traffic; state = CG_STATE_ROLLED_BACK;
+        }
         out->traffic_current = cur; out->traffic_prev = prev; out->state = state;
         out->n_promotions = n_prom; out->n_evals = n_eval; out->last_tick = last;
     }

@@ -259,15 +259,17 @@ def should_promote(new: dict, old: dict, thresholds: dict) -> bool:
     return ok
 
 
-STATE_IN_PROGRESS, STATE_COMPLETE, STATE_ABORTED, STATE_NO_CANARY = 0, 1, 2, 3
+STATE_IN_PROGRESS, STATE_COMPLETE, STATE_ABORTED, STATE_NO_CANARY, STATE_ROLLED_BACK = 0, 1, 2, 3, 4
 
 
 def replay_schedule(gate_bits: Sequence[bool], start_tick: int = 0, init_current: int = 10,
                     max_traffic: int = 100, step: int = 10, interval_ticks: int = 6,
                     max_attempts: int = 10, attempt_delay_ticks: int = 1,
-                    has_previous: bool = True) -> dict:
+                    has_previous: bool = True, rollback: bool = False) -> dict:
     """mlflow_operator.py:184-191 and :290-361 as a pure function over gate
-    bits sampled on the tick grid.  Returns the decision record."""
+    bits sampled on the tick grid.  Returns the decision record.
+    rollback=True is the opt-in extension for the placeholder the reference leaves at :345:
+    after the 10th failed attempt all traffic goes back to the old version."""
     if not has_previous:                                          # :188-191, :289
         return dict(cur=100, prev=0, state=STATE_NO_CANARY, n_promotions=0,
                     n_evals=0, last_tick=-1)
@@ -297,5 +299,7 @@ def replay_schedule(gate_bits: Sequence[bool], start_tick: int = 0, init_current
         tick += interval_ticks                                    # :352
     if cur == max_traffic:                                        # :355
         state = STATE_COMPLETE
+    if state == STATE_ABORTED and rollback:                       # not in the reference (:345 is a comment)
+        cur, prev, state = 0, max_traffic, STATE_ROLLED_BACK
     return dict(cur=cur, prev=prev, state=state, n_promotions=n_prom,
                 n_evals=n_eval, last_tick=last)

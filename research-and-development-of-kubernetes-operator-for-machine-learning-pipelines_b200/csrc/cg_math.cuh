@@ -191,6 +191,9 @@ CG_DEVINL cg_decision replay_schedule(BitFn gate_bit, bool has_previous, int sta
         tick += p.interval_ticks;                                    // :352
     }
     if (cur == p.max_traffic) state = CG_STATE_COMPLETE;             // :355
+    if (state == CG_STATE_ABORTED && p.on_abort == CG_ABORT_ROLLBACK) {   // opt-in, not in the reference (:345)
+        cur = 0; prev = p.max_traffic; state = CG_STATE_ROLLED_BACK;
+    }
     d.traffic_current = cur; d.traffic_prev = prev; d.state = state;
     d.n_promotions = n_prom; d.n_evals = n_eval; d.last_tick = last;
     return d;
@@ -231,6 +234,9 @@ CG_DEVINL cg_decision replay_schedule_bits(const uint32_t* bits, int n_words, bo
         }
     }
     if (cur == p.max_traffic) state = CG_STATE_COMPLETE;               // :355
+    if (state == CG_STATE_ABORTED && p.on_abort == CG_ABORT_ROLLBACK) {   // opt-in, not in the reference (:345)
+        cur = 0; prev = p.max_traffic; state = CG_STATE_ROLLED_BACK;
+    }
     cg_decision d;
     d.traffic_current = cur; d.traffic_prev = prev; d.state = state;
     d.n_promotions = n_prom; d.n_evals = n_eval; d.last_tick = last;

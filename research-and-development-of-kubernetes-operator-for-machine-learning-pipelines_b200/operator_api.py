@@ -180,11 +180,15 @@ def canary_schedule(gate_bits: torch.Tensor, params: CgParams, has_previous=None
 def decisions_to_predictor_traffic(decisions: torch.Tensor, current_versions: Sequence,
                                    previous_versions: Sequence):
     """Decision records -> the `predictors[*].traffic` values the operator patches into each
-    SeldonDeployment (:320-328), with the old predictor dropped at 100 % (:355-358)."""
+    SeldonDeployment (:320-328), with the old predictor dropped at 100 % (:355-358).  With the
+    opt-in rollback policy (params.make_params(rollback=True)) a rolled-back canary collapses to the
+    OLD predictor alone, the mirror image of completion."""
     rows = decisions.cpu().tolist()
     out = []
     for (cur, prev, state, *_), cv, pv in zip(rows, current_versions, previous_versions):
-        if pv is None or state == 1 or state == 3:
+        if pv is not None and state == 4:
+            out.append({"state": STATE_NAMES[state], "predictors": [{"name": f"v{pv}", "traffic": 100}]})
+        elif pv is None or state == 1 or state == 3:
             out.append({"state": STATE_NAMES[state], "predictors": [{"name": f"v{cv}", "traffic": 100}]})
         else:
             out.append({"state": STATE_NAMES[state],

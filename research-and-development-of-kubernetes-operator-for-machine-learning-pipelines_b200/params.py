@@ -18,8 +18,9 @@ MAX_SCALAR, MAX_Q = 16, 4
 M_ERROR_RESPONSES, M_ERROR_RATE, M_LATENCY_AVG, M_REQUEST_COUNT, M_FEEDBACK_COUNT, M_EXTRA = 0, 1, 2, 3, 4, 5
 V_QUANTILE, V_ERROR_RATE, V_LATENCY_AVG = 1, 2, 4
 G_P95_OK, G_ERR_OK, G_AVG_OK, G_AVAILABLE, G_PROMOTE = 1, 2, 4, 8, 0x80
-STATE_IN_PROGRESS, STATE_COMPLETE, STATE_ABORTED, STATE_NO_CANARY = 0, 1, 2, 3
-STATE_NAMES = {0: "in_progress", 1: "complete", 2: "aborted", 3: "no_canary"}
+STATE_IN_PROGRESS, STATE_COMPLETE, STATE_ABORTED, STATE_NO_CANARY, STATE_ROLLED_BACK = 0, 1, 2, 3, 4
+STATE_NAMES = {0: "in_progress", 1: "complete", 2: "aborted", 3: "no_canary", 4: "rolled_back"}
+ABORT_FREEZE, ABORT_ROLLBACK = 0, 1
 
 # mlflow_operator.py:175-179
 REFERENCE_THRESHOLDS = {"latency_95th": 0.05, "error_rate": 0.02, "latency_avg": 0.05}
@@ -41,7 +42,7 @@ class CgParams(C.Structure):
         ("init_current", C.c_int32), ("max_traffic", C.c_int32), ("step", C.c_int32),
         ("interval_ticks", C.c_int32), ("max_attempts", C.c_int32),
         ("attempt_delay_ticks", C.c_int32), ("start_tick", C.c_int32),
-        ("reserved", C.c_int32),
+        ("reserved", C.c_int32), ("on_abort", C.c_int32),
     ]
 
     @property
@@ -86,9 +87,11 @@ def make_params(n_samples: int = 240, n_scalar: int = 4, n_buckets: int = 64,
                 gate_q: int = 0, thresholds: Optional[dict] = None, checks: int = 7,
                 init_current: int = 10, max_traffic: int = 100, step: int = 10,
                 interval_s: int = 60, max_attempts: int = 10, attempt_delay_s: int = 10,
-                start_tick: int = 0) -> CgParams:
+                start_tick: int = 0, rollback: bool = False) -> CgParams:
     """Build a parameter block.  With no arguments: the reference's constants on
-    BASELINE.json's full layout (1 h of 15 s scrapes, ticks every 10 s)."""
+    BASELINE.json's full layout (1 h of 15 s scrapes, ticks every 10 s).
+    rollback=True opts into sending all traffic back to the old version after max_attempts
+    failures (state ROLLED_BACK); the reference freezes the weights there (:341-349)."""
     p = CgParams()
     p.struct_bytes = C.sizeof(CgParams)
     p.dtype = dtype
@@ -132,4 +135,5 @@ def make_params(n_samples: int = 240, n_scalar: int = 4, n_buckets: int = 64,
     p.max_attempts = max_attempts
     p.attempt_delay_ticks = attempt_delay_s * 1000 // tick_step_ms
     p.start_tick = start_tick
+    p.on_abort = ABORT_ROLLBACK if rollback else ABORT_FREEZE
     return p
