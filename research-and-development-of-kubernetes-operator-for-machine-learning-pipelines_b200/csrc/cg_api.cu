@@ -183,7 +183,9 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
     const int threads = a.consumer_warps * 32;
     int per_sm = 1, slots = 0;
-    for (int c = (a.consumer_warps <= 4 ? 4 : 1); c >= 1; --c) {
+    int c_max = a.consumer_warps <= 4 ? 4 : 1;
+    if (const char* e = getenv("CG_STREAM_PER_SM")) { int v = atoi(e); if (v >= 1 && v < c_max) c_max = v; }   // tuning aid
+    for (int c = c_max; c >= 1; --c) {
         if (c * threads > 2048) continue;
         const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
         if (budget <= fixed) continue;
