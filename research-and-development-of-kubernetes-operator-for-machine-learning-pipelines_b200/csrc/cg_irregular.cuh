@@ -36,15 +36,26 @@ struct IrregularArgs {
     uint32_t off_ts, off_cnt, off_le, off_stash, off_stash_valid, off_bits, off_bar, smem_bytes;
 };
 
+// Extrapolation terms of a window (Appendix A steps 3 and 5).  They depend on the time stamps alone,
+// and the series of one target are scraped together, so a thread keeps the terms of the last window
+// it saw and reuses them while (first, last, count) stay the same: same operations, done once.
+struct WindowTerms {
+    int first_t, last_t, n;      // the window they belong to; n = 0: none yet
+    int a;                       // index of its first sample (search hint for the next row)
+    double d_start, sampled, thr, half_avg, end_term;
+    double f;                    // ext / sampled when the zero-point clamp does not fire
+};
+
 // increase() of one series at one tick from its own time stamps (Appendix A steps 1-6, the same
 // operations in the same order as oracle/promql_oracle.c increase_core).  false: no output.
 template <typename T>
 __device__ bool irregular_increase(const T* __restrict__ v, const int32_t* __restrict__ ts, int cnt, int t0, float inv,
-                                   int t, int lo, bool left_open, double& inc) {
+                                   int t, int lo, bool left_open, WindowTerms& wt, double& inc) {
     if (cnt < 2) return false;
-    // a = first sample inside the window.  Start from where a regular grid would put it (t0 = first
-    // time stamp of the row, inv = samples per ms) and walk: O(1) for near-regular scrapes, O(gap) otherwise.
-    int a = (int)((float)(lo - t0) * inv);
+    // a = first sample inside the window.  Start where the previous row had it (same scrape times), or
+    // where a regular grid would put it (t0 = first time stamp of the row, inv = samples per ms), and
+    // walk: O(1) for near-regular scrapes, O(gap) otherwise.
+    int a = wt.n ? wt.a : (int)((float)(lo - t0) * inv);
     a = a < 0 ? 0 : (a > cnt ? cnt : a);
     while (a > 0 && !(left_open ? ts[a - 1] <= lo : ts[a - 1] < lo)) --a;
     while (a < cnt && (left_open ? ts[a] <= lo : ts[a] < lo)) ++a;
@@ -62,20 +73,38 @@ __device__ bool irregular_increase(const T* __restrict__ v, const int32_t* __res
         prev = x;
     }
     const int first_t = ts[a], last_t = ts[b];
-    // (division by a constant: div_const gives the correctly rounded quotient, as `/` does)
-    double d_start = div_const((double)(first_t - lo), 1000.0, 1e-3);          // step 3
-    const double d_end = div_const((double)(t - last_t), 1000.0, 1e-3);
-    const double sampled = div_const((double)(last_t - first_t), 1000.0, 1e-3);
-    const double avg = sampled / (double)(n - 1);
-    if (result > 0 && first_v >= 0) {                          // step 4
-        const double d_zero = sampled * (first_v / result);
-        if (d_zero < d_start) d_start = d_zero;
+    if (!(wt.n == n && wt.first_t == first_t && wt.last_t == last_t)) {
+        // (division by a constant: div_const gives the correctly rounded quotient, as `/` does)
+        wt.d_start = div_const((double)(first_t - lo), 1000.0, 1e-3);          // step 3
+        const double d_end = div_const((double)(t - last_t), 1000.0, 1e-3);
+        wt.sampled = div_const((double)(last_t - first_t), 1000.0, 1e-3);
+        const double avg = wt.sampled / (double)(n - 1);
+        wt.thr = avg * 1.1;                                    // step 5
+        wt.half_avg = avg / 2;
+        wt.end_term = (d_end < wt.thr) ? d_end : wt.half_avg;
+        double ext = wt.sampled;
+        ext += (wt.d_start < wt.thr) ? wt.d_start : wt.half_avg;
+        ext += wt.end_term;
+        wt.f = ext / wt.sampled;
+        wt.first_t = first_t; wt.last_t = last_t; wt.n = n;
     }
-    const double thr = avg * 1.1;                              // step 5
-    double ext = sampled;
-    ext += (d_start < thr) ? d_start : avg / 2;
-    ext += (d_end < thr) ? d_end : avg / 2;
-    inc = result * (ext / sampled);                            // step 6
+    wt.a = a;
+    if (result > 0 && first_v >= 0) {                          // step 4: the zero-point clamp
+        // d_zero = sampled * (first_v / result) < d_start is impossible when first_v * sampled exceeds
+        // d_start * result by more than the roundings involved: one comparison instead of a division
+        const double lhs = first_v * wt.sampled, rhs = (wt.d_start * result) * (1.0 + 1e-12);
+        if (!(lhs >= rhs && lhs < 1e300 && rhs > 1e-290)) {
+            const double d_zero = wt.sampled * (first_v / result);
+            if (d_zero < wt.d_start) {
+                double ext = wt.sampled;
+                ext += (d_zero < wt.thr) ? d_zero : wt.half_avg;
+                ext += wt.end_term;
+                inc = result * (ext / wt.sampled);             // step 6
+                return true;
+            }
+        }
+    }
+    inc = result * wt.f;                                       // step 6
     return true;
 }
 
@@ -90,12 +119,14 @@ __device__ void eval_tick_irregular(const T* __restrict__ sc_rows, const T* __re
     const int t = p.tick0_ms + tick * p.tick_step_ms, lo = t - p.window_ms;
     const bool lopen = p.left_open != 0;
     uint8_t valid = 0;
+    WindowTerms wt;
+    wt.n = 0;
     double sums[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
     unsigned have = 0;
     for (int k = 0; k < p.n_scalar; ++k) {      // Q2..Q6: sum(increase(...)) or on() vector(0)
         double inc;
         if (!irregular_increase(sc_rows + (size_t)k * pitch, ts_sc + (size_t)k * pitch, cnt_sc[k], t0_row[k], inv_row[k],
-                                t, lo, lopen, inc))
+                                t, lo, lopen, wt, inc))
             continue;
         const unsigned role = p.scalar_role[k];
 #pragma unroll
@@ -110,72 +141,127 @@ __device__ void eval_tick_irregular(const T* __restrict__ sc_rows, const T* __re
     // Q1: histogram_quantile over the buckets that have output, in `le` order
     for (int j = 0; j < nq; ++j) m[j] = NAN;
     const double range_s = (double)p.window_ms / 1000.0, rc_range = 1.0 / range_s;
-    // pass 1: which buckets are present, the fixed count of the highest one (the observations)
-    int n_present = 0, last_b = -1, second_b = -1;
-    double mx = 0.0, obs = 0.0;
-    for (int b = 0; b < B; ++b) {
-        double inc;
-        if (!irregular_increase(bk_rows + (size_t)b * pitch, ts_bk + (size_t)b * pitch, cnt_bk[b], t0_row[K + b],
-                                inv_row[K + b], t, lo, lopen, inc))
-            continue;
-        double c = div_const(inc, range_s, rc_range);
-        if (n_present == 0) mx = c;
-        else if (c > mx) mx = c;
-        else if (c < mx) c = mx;
-        obs = c;
-        second_b = last_b;
-        last_b = b;
-        ++n_present;
-    }
-    if (n_present > 0) {
-        valid |= CG_V_QUANTILE;                                // non-empty vector (:369-370)
-        const bool top_inf = isinf(le[last_b]) && le[last_b] > 0;   // highest bound present must be +Inf
-        bool need_scan = false;
-        bool found[CG_MAX_Q];
-        double rank[CG_MAX_Q];
-        for (int j = 0; j < nq; ++j) {
-            const double q = p.q[j];
-            found[j] = true;
-            if (isnan(q)) m[j] = NAN;
-            else if (q < 0) m[j] = -INFINITY;
-            else if (q > 1) m[j] = INFINITY;
-            else if (!top_inf || n_present < 2) m[j] = NAN;    // Appendix A step 2
-            else if (obs == 0) m[j] = NAN;                     // step 4
-            else { found[j] = false; need_scan = true; rank[j] = q * obs; }   // step 5
-        }
-        if (need_scan) {
-            // pass 2: first present bucket below the highest one whose fixed count reaches the rank
-            double prevc = 0.0, prev_le = 0.0;
-            int idx = 0;
-            mx = 0.0;
-            for (int b = 0; b < last_b; ++b) {
+    // Usual shape first, in ONE pass: the +Inf bucket has output, and (speculation, checked at the end)
+    // it holds the observations, i.e. no lower bucket exceeds it after the monotonic fix.
+    bool done = false;
+    if (B >= 1 && isinf(le[B - 1]) && le[B - 1] > 0) {
+        double inc_inf;
+        if (irregular_increase(bk_rows + (size_t)(B - 1) * pitch, ts_bk + (size_t)(B - 1) * pitch, cnt_bk[B - 1],
+                               t0_row[K + B - 1], inv_row[K + B - 1], t, lo, lopen, wt, inc_inf)) {
+            const double c_inf = div_const(inc_inf, range_s, rc_range);
+            bool found[CG_MAX_Q];
+            double rank[CG_MAX_Q], cand[CG_MAX_Q];
+            for (int j = 0; j < nq; ++j) { found[j] = false; rank[j] = p.q[j] * c_inf; cand[j] = NAN; }   // step 5
+            double prevc = 0.0, prev_le = 0.0, mx = 0.0;
+            int idx = 0, second_b = -1;
+            for (int b = 0; b < B - 1; ++b) {
                 double inc;
                 if (!irregular_increase(bk_rows + (size_t)b * pitch, ts_bk + (size_t)b * pitch, cnt_bk[b], t0_row[K + b],
-                                        inv_row[K + b], t, lo, lopen, inc))
+                                        inv_row[K + b], t, lo, lopen, wt, inc))
                     continue;
                 double c = div_const(inc, range_s, rc_range);
                 if (idx == 0) mx = c;
                 else if (c > mx) mx = c;
                 else if (c < mx) c = mx;
-                bool all = true;
                 for (int j = 0; j < nq; ++j) {
-                    if (!found[j] && c >= rank[j]) {
+                    if (!found[j] && c >= rank[j]) {           // (never true for a NaN rank)
                         found[j] = true;
-                        if (idx == 0 && le[b] <= 0) m[j] = le[b];             // step 6
+                        if (idx == 0 && le[b] <= 0) cand[j] = le[b];              // step 6
                         else {
                             double start = 0.0, end = le[b], cc = c, rk = rank[j];   // step 7
                             if (idx > 0) { start = prev_le; cc -= prevc; rk -= prevc; }
-                            m[j] = start + (end - start) * (rk / cc);
+                            cand[j] = start + (end - start) * (rk / cc);
                         }
                     }
-                    all = all && found[j];
                 }
                 prevc = c;
                 prev_le = le[b];
+                second_b = b;
                 ++idx;
-                if (all) break;
             }
-            for (int j = 0; j < nq; ++j) if (!found[j]) m[j] = le[second_b];   // b == n-1: bound of the bucket below +Inf
+            if (!(idx > 0 && mx > c_inf)) {                    // the +Inf bucket is the maximum: observations = c_inf
+                done = true;
+                valid |= CG_V_QUANTILE;                        // non-empty vector (:369-370)
+                for (int j = 0; j < nq; ++j) {
+                    const double q = p.q[j];
+                    if (isnan(q)) m[j] = NAN;
+                    else if (q < 0) m[j] = -INFINITY;
+                    else if (q > 1) m[j] = INFINITY;
+                    else if (idx < 1) m[j] = NAN;              // fewer than 2 buckets (Appendix A step 2)
+                    else if (c_inf == 0) m[j] = NAN;           // step 4
+                    else m[j] = found[j] ? cand[j] : le[second_b];   // not found: bound of the bucket below +Inf
+                }
+            }
+        }
+    }
+    if (!done) {
+        // pass 1: which buckets are present, the fixed count of the highest one (the observations)
+        int n_present = 0, last_b = -1, second_b = -1;
+        double mx = 0.0, obs = 0.0;
+        for (int b = 0; b < B; ++b) {
+            double inc;
+            if (!irregular_increase(bk_rows + (size_t)b * pitch, ts_bk + (size_t)b * pitch, cnt_bk[b], t0_row[K + b],
+                                    inv_row[K + b], t, lo, lopen, wt, inc))
+                continue;
+            double c = div_const(inc, range_s, rc_range);
+            if (n_present == 0) mx = c;
+            else if (c > mx) mx = c;
+            else if (c < mx) c = mx;
+            obs = c;
+            second_b = last_b;
+            last_b = b;
+            ++n_present;
+        }
+        if (n_present > 0) {
+            valid |= CG_V_QUANTILE;                                // non-empty vector (:369-370)
+            const bool top_inf = isinf(le[last_b]) && le[last_b] > 0;   // highest bound present must be +Inf
+            bool need_scan = false;
+            bool found[CG_MAX_Q];
+            double rank[CG_MAX_Q];
+            for (int j = 0; j < nq; ++j) {
+                const double q = p.q[j];
+                found[j] = true;
+                if (isnan(q)) m[j] = NAN;
+                else if (q < 0) m[j] = -INFINITY;
+                else if (q > 1) m[j] = INFINITY;
+                else if (!top_inf || n_present < 2) m[j] = NAN;    // Appendix A step 2
+                else if (obs == 0) m[j] = NAN;                     // step 4
+                else { found[j] = false; need_scan = true; rank[j] = q * obs; }   // step 5
+            }
+            if (need_scan) {
+                // pass 2: first present bucket below the highest one whose fixed count reaches the rank
+                double prevc = 0.0, prev_le = 0.0;
+                int idx = 0;
+                mx = 0.0;
+                for (int b = 0; b < last_b; ++b) {
+                    double inc;
+                    if (!irregular_increase(bk_rows + (size_t)b * pitch, ts_bk + (size_t)b * pitch, cnt_bk[b], t0_row[K + b],
+                                            inv_row[K + b], t, lo, lopen, wt, inc))
+                        continue;
+                    double c = div_const(inc, range_s, rc_range);
+                    if (idx == 0) mx = c;
+                    else if (c > mx) mx = c;
+                    else if (c < mx) c = mx;
+                    bool all = true;
+                    for (int j = 0; j < nq; ++j) {
+                        if (!found[j] && c >= rank[j]) {
+                            found[j] = true;
+                            if (idx == 0 && le[b] <= 0) m[j] = le[b];             // step 6
+                            else {
+                                double start = 0.0, end = le[b], cc = c, rk = rank[j];   // step 7
+                                if (idx > 0) { start = prev_le; cc -= prevc; rk -= prevc; }
+                                m[j] = start + (end - start) * (rk / cc);
+                            }
+                        }
+                        all = all && found[j];
+                    }
+                    prevc = c;
+                    prev_le = le[b];
+                    ++idx;
+                    if (all) break;
+                }
+                for (int j = 0; j < nq; ++j) if (!found[j]) m[j] = le[second_b];   // b == n-1: bound of the bucket below +Inf
+            }
         }
     }
     m[nq + CG_M_ERROR_RESPONSES] = err;

@@ -57,6 +57,10 @@ CONFIGS = {
     "three_quantiles_k5": dict(make=dict(n_samples=80, n_scalar=5, n_buckets=12, quantiles=(0.5, 0.95, 0.99), gate_q=2),
                                n=32, irr=dict(seed=7)),
     "fp32": dict(make=dict(dtype=P.CG_F32, n_samples=120, n_buckets=16), n=32, irr=dict(seed=8)),
+    # per-series misses: the +Inf bucket often has a shorter window than the buckets below it, so the
+    # monotonic fix raises the observations (the kernel's one-pass speculation fails and it re-scans)
+    "series_level_misses": dict(make=dict(n_samples=80, n_buckets=6), n=32,
+                                irr=dict(seed=10, series_miss_prob=0.25, miss_prob=0.0, gap_prob=0.0)),
     "long_window": dict(make=dict(period_ms=30000, elapsed_time=300, n_samples=120, n_buckets=8), n=24,
                         irr=dict(seed=9, jitter_ms=5000)),
 }
