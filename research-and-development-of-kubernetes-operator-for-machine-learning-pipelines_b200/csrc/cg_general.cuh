@@ -31,6 +31,22 @@ struct GeneralArgs {
     uint32_t off_le, off_stash, off_stash_valid, off_bits, off_bar, smem_bytes;
 };
 
+// increase() of one series with the tick's extrapolation factor computed once (f = ext / sampled
+// for the unclamped d_start: it depends on the time stamps alone) and one multiply test in front of
+// the zero-point division: d_zero = sampled * (first_v / result) < d_start is impossible when
+// first_v * sampled exceeds d_start * result by more than the roundings involved.  Same operations
+// as extrapolate() whenever the clamp can fire; the same value otherwise.
+template <typename T>
+CG_DEVINL double series_increase_f(const T* __restrict__ row, const TickGeom& g, double f) {
+    double first_v;
+    const double result = window_result(row + g.i0, g.n, first_v);
+    if (result > 0 && first_v >= 0) {
+        const double lhs = first_v * g.sampled, rhs = (g.d_start * result) * (1.0 + 1e-12);
+        if (!(lhs >= rhs && lhs < 1e300 && rhs > 1e-290)) return extrapolate(result, first_v, g);
+    }
+    return result * f;
+}
+
 // Everything get_model_metrics returns for one (pair, version, tick), from a resident tile.
 template <typename T>
 __device__ void eval_tick_resident(const T* __restrict__ sc_rows, const T* __restrict__ bk_rows,
@@ -40,9 +56,16 @@ __device__ void eval_tick_resident(const T* __restrict__ sc_rows, const T* __res
     uint8_t valid = 0;
     double sums[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
     unsigned have = 0;
+    double f = 0.0;               // Appendix A steps 5-6 without the clamp, once per tick
+    if (g.n >= 2) {
+        double ext = g.sampled;
+        ext += (g.d_start < g.thr) ? g.d_start : g.avg / 2;
+        ext += g.end_term;
+        f = ext / g.sampled;
+    }
     if (g.n >= 2) {   // Q2..Q6: sum(increase(...)) or on() vector(0)  (:375,:383,:393,:397,:410)
         for (int k = 0; k < p.n_scalar; ++k) {
-            const double inc = series_increase(sc_rows + (size_t)k * p.row_pitch, g);
+            const double inc = series_increase_f(sc_rows + (size_t)k * p.row_pitch, g, f);
             const unsigned role = p.scalar_role[k];
 #pragma unroll
             for (int r = 0; r < 5; ++r)
@@ -59,7 +82,7 @@ __device__ void eval_tick_resident(const T* __restrict__ sc_rows, const T* __res
     const int B = p.n_buckets;
     if (B > 0 && g.n >= 2) {
         valid |= CG_V_QUANTILE;                       // non-empty vector (:369-370)
-        const double range_s = (double)p.window_ms / 1000.0;
+        const double range_s = (double)p.window_ms / 1000.0, rc_range = 1.0 / range_s;
         const bool top_inf = isinf(le[B - 1]) && le[B - 1] > 0;
         bool need_scan = false;
         double rank[CG_MAX_Q];
@@ -74,44 +97,74 @@ __device__ void eval_tick_resident(const T* __restrict__ sc_rows, const T* __res
             else { found[j] = false; need_scan = true; }
         }
         if (need_scan) {
-            // pass 1: observations = last count after the monotonic fix (step 3-4)
-            double mx = 0.0, obs = 0.0;
-            for (int b = 0; b < B; ++b) {
-                double c = series_increase(bk_rows + (size_t)b * p.row_pitch, g) / range_s;
+            // One pass in the usual case: the +Inf bucket first, speculating that it holds the
+            // observations (no lower bucket exceeds it after the monotonic fix, step 3-4); checked below.
+            const double c_inf = div_const(series_increase_f(bk_rows + (size_t)(B - 1) * p.row_pitch, g, f), range_s, rc_range);
+            double cand[CG_MAX_Q];
+            bool hit[CG_MAX_Q];
+            for (int j = 0; j < nq; ++j) { rank[j] = p.q[j] * c_inf; cand[j] = NAN; hit[j] = found[j]; }   // step 5
+            double prevc = 0.0, mx = 0.0;
+            for (int b = 0; b < B - 1; ++b) {
+                double c = div_const(series_increase_f(bk_rows + (size_t)b * p.row_pitch, g, f), range_s, rc_range);
                 if (b == 0) mx = c;
                 else if (c > mx) mx = c;
                 else if (c < mx) c = mx;
-                obs = c;
+                for (int j = 0; j < nq; ++j) {
+                    if (!hit[j] && c >= rank[j]) {
+                        hit[j] = true;
+                        if (b == 0 && le[0] <= 0) cand[j] = le[0];            // step 6
+                        else {
+                            double start = 0.0, end = le[b], cc = c, rk = rank[j];   // step 7
+                            if (b > 0) { start = le[b - 1]; cc -= prevc; rk -= prevc; }
+                            cand[j] = start + (end - start) * (rk / cc);
+                        }
+                    }
+                }
+                prevc = c;
             }
-            if (obs == 0) {
-                for (int j = 0; j < nq; ++j) if (!found[j]) { m[j] = NAN; found[j] = true; }
+            if (!(mx > c_inf)) {      // the +Inf bucket is the maximum: observations = c_inf
+                for (int j = 0; j < nq; ++j)
+                    if (!found[j]) m[j] = (c_inf == 0) ? NAN : hit[j] ? cand[j] : le[B - 2];   // step 4; found; b == n-1
             } else {
-                for (int j = 0; j < nq; ++j) rank[j] = p.q[j] * obs;          // step 5
-                // pass 2: first bucket in [0, B-2] whose fixed count reaches the rank
-                double prevc = 0.0;
-                mx = 0.0;
-                for (int b = 0; b < B - 1; ++b) {
-                    double c = series_increase(bk_rows + (size_t)b * p.row_pitch, g) / range_s;
+                // pass 1: observations = last count after the monotonic fix (step 3-4)
+                double mx = 0.0, obs = 0.0;
+                for (int b = 0; b < B; ++b) {
+                    double c = div_const(series_increase_f(bk_rows + (size_t)b * p.row_pitch, g, f), range_s, rc_range);
                     if (b == 0) mx = c;
                     else if (c > mx) mx = c;
                     else if (c < mx) c = mx;
-                    bool all = true;
-                    for (int j = 0; j < nq; ++j) {
-                        if (!found[j] && c >= rank[j]) {
-                            found[j] = true;
-                            if (b == 0 && le[0] <= 0) m[j] = le[0];           // step 6
-                            else {
-                                double start = 0.0, end = le[b], cc = c, rk = rank[j];   // step 7
-                                if (b > 0) { start = le[b - 1]; cc -= prevc; rk -= prevc; }
-                                m[j] = start + (end - start) * (rk / cc);
-                            }
-                        }
-                        all = all && found[j];
-                    }
-                    prevc = c;
-                    if (all) break;
+                    obs = c;
                 }
-                for (int j = 0; j < nq; ++j) if (!found[j]) m[j] = le[B - 2];  // b == n-1
+                if (obs == 0) {
+                    for (int j = 0; j < nq; ++j) if (!found[j]) { m[j] = NAN; found[j] = true; }
+                } else {
+                    for (int j = 0; j < nq; ++j) rank[j] = p.q[j] * obs;          // step 5
+                    // pass 2: first bucket in [0, B-2] whose fixed count reaches the rank
+                    double prevc = 0.0;
+                    mx = 0.0;
+                    for (int b = 0; b < B - 1; ++b) {
+                        double c = div_const(series_increase_f(bk_rows + (size_t)b * p.row_pitch, g, f), range_s, rc_range);
+                        if (b == 0) mx = c;
+                        else if (c > mx) mx = c;
+                        else if (c < mx) c = mx;
+                        bool all = true;
+                        for (int j = 0; j < nq; ++j) {
+                            if (!found[j] && c >= rank[j]) {
+                                found[j] = true;
+                                if (b == 0 && le[0] <= 0) m[j] = le[0];           // step 6
+                                else {
+                                    double start = 0.0, end = le[b], cc = c, rk = rank[j];   // step 7
+                                    if (b > 0) { start = le[b - 1]; cc -= prevc; rk -= prevc; }
+                                    m[j] = start + (end - start) * (rk / cc);
+                                }
+                            }
+                            all = all && found[j];
+                        }
+                        prevc = c;
+                        if (all) break;
+                    }
+                    for (int j = 0; j < nq; ++j) if (!found[j]) m[j] = le[B - 2];  // b == n-1
+                }
             }
         }
     }
