@@ -7,7 +7,7 @@
 // (int32 ms) and the per-row sample counts are brought into shared memory (TMA bulk copies on one
 // mbarrier), then one thread per tick evaluates the six queries of get_model_metrics
 // (mlflow_operator.py:367-410).  What differs is the window: each series finds its own
-// [first, last] samples by binary search in its time stamps, the extrapolation terms
+// [first, last] samples by a short walk from a hint in its time stamps, the extrapolation terms
 // (Appendix A steps 3-5) are computed from those time stamps -- so the avg*1.1 threshold branch
 // is live -- and a series with fewer than 2 samples in the window yields no output: it drops out
 // of its sum, and a bucket without output is absent from the vector histogram_quantile sees.
