@@ -59,8 +59,10 @@ __device__ bool irregular_increase(const T* __restrict__ v, const int32_t* __res
     a = a < 0 ? 0 : (a > cnt ? cnt : a);
     while (a > 0 && !(left_open ? ts[a - 1] <= lo : ts[a - 1] < lo)) --a;
     while (a < cnt && (left_open ? ts[a] <= lo : ts[a] < lo)) ++a;
-    // b = last sample at or before the tick
-    int b = a - 1;
+    // b = last sample at or before the tick: start from the length of the previous row's window
+    int b = a - 1 + (wt.n ? wt.n : 0);
+    if (b > cnt - 1) b = cnt - 1;
+    while (b >= a && ts[b] > t) --b;
     while (b + 1 < cnt && ts[b + 1] <= t) ++b;
     const int n = b - a + 1;
     if (n < 2) return false;                                   // step 1
