@@ -85,6 +85,54 @@ class SeriesStore:
         return out
 
 
+class IrregularSeriesStore(SeriesStore):
+    """The same store for scrapes that are not a perfect grid: every series
+    has its own int32 ms time stamps and sample count (synth.IrregularBatch / ingest.HostIrregular
+    layout).  get_model_metrics / should_promote_model / evaluate_canaries work on it unchanged."""
+
+    def __init__(self, scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, params: CgParams,
+                 index: Optional[Dict] = None, now_ms: Optional[int] = None):
+        self.scalars, self.buckets, self.le = scalars, buckets, le
+        self.ts_scalars, self.ts_buckets = ts_scalars, ts_buckets
+        self.cnt_scalars, self.cnt_buckets = cnt_scalars, cnt_buckets
+        self.phase = None
+        self.params = params
+        self.index = index or {}
+        self.now_ms = params.tick0_ms if now_ms is None else now_ms
+        self._cache = {}
+
+    @property
+    def n_pairs(self) -> int:
+        return int(self.cnt_scalars.shape[0])
+
+    @classmethod
+    def from_host(cls, batch, device="cuda", index=None, now_ms=None) -> "IrregularSeriesStore":
+        dev = torch.device(device)
+        t = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+        return cls(t(batch.scalars), t(batch.buckets), t(batch.ts_scalars), t(batch.ts_buckets),
+                   t(batch.cnt_scalars), t(batch.cnt_buckets), t(batch.le), batch.params,
+                   index=index if index is not None else getattr(batch, "index", None), now_ms=now_ms)
+
+    def _series(self, rows=slice(None)):
+        return (self.scalars[rows], self.buckets[rows], self.ts_scalars[rows], self.ts_buckets[rows],
+                self.cnt_scalars[rows], self.cnt_buckets[rows], self.le)
+
+    def _instant(self, row: int, elapsed_time: int):
+        key = (row, self.now_ms, int(elapsed_time))
+        hit = self._cache.get(key)
+        if hit is not None:
+            return hit
+        p = self.params.copy()
+        p.window_ms = int(elapsed_time * 1000)
+        p.tick0_ms = self.now_ms
+        p.n_ticks = 1
+        _, metrics, valid = engine.eval_irregular(*self._series(slice(row, row + 1)), p, want_metrics=True)
+        out = (metrics[0, :, 0, :].cpu(), valid[0, :, 0].cpu(), p)
+        self._cache.clear()
+        self._cache[key] = out
+        return out
+
+
 def _record_to_dict(rec, valid: int, p: CgParams) -> dict:
     """Metric record -> the dict get_model_metrics builds (:364-417)."""
     nq = p.n_q
@@ -167,6 +215,13 @@ def evaluate_canaries(store: SeriesStore, has_previous: Optional[torch.Tensor] =
     """Run the whole canary (metrics on the dense tick grid -> gate -> step loop) for every
     row of the store.  -> decisions [N, 6] int32: traffic_current, traffic_prev, state,
     n_promotions, n_evals, last_tick."""
+    if isinstance(store, IrregularSeriesStore):
+        res = engine.eval_irregular(*store._series(), store.params, has_previous=has_previous,
+                                    start_tick=start_tick, want_bits=want_bits)
+        if out is not None:
+            out.copy_(res[0] if want_bits else res)
+            return (out, res[1]) if want_bits else out
+        return res
     return engine.eval_fused(store.scalars, store.buckets, store.le, store.phase, store.params,
                              has_previous=has_previous, start_tick=start_tick,
                              want_bits=want_bits, out=out)

@@ -112,3 +112,37 @@ def test_ingested_prometheus_answers_drive_the_same_decisions():
         got = api.get_model_metrics(store, f"model-{i:03d}", "v2", "prod")
         for k, v in t["new"].items():
             assert same_float(got[k], fdec(v)), (i, k)
+
+
+def test_drop_in_signatures_on_irregular_series_reproduce_reference_runs():
+    """Same loop, on scrapes that are not a grid: goldens from the unmodified reference
+    (tests/golden/ref_irregular_cases.*)."""
+    from golden_util import load_irregular_batches
+    batches, cases = load_irregular_batches()
+    ib = batches["irr"]
+    p = ib.params
+    store = api.IrregularSeriesStore.from_host(ib)
+    for case in (c for c in cases if c["geometry"] == "irr"):
+        i = case["pair"]
+        store.register("m", "ns", i, new_version="2", old_version="1")
+        for t in case["ticks"][:8]:
+            store.set_time(p.tick0_ms + t["tick"] * p.tick_step_ms)
+            dicts = {}
+            for key, pred in (("new", "v2"), ("old", "v1")):
+                got = dicts[key] = api.get_model_metrics(store, "m", pred, "ns")
+                for k, v in t[key].items():
+                    assert same_float(got[k], fdec(v)), (i, t["tick"], key, k, got[k], fdec(v))
+            assert api.should_promote_model(dicts["new"], dicts["old"], dict(P.REFERENCE_THRESHOLDS), LOG) == t["promote"]
+        run = case["runs"][0]
+        store.set_time(p.tick0_ms)
+        cur, prev, n_evals, end_ms = run_loop_like_the_reference(store, "m", "ns", "2", "1")
+        if run["state"] == P.STATE_COMPLETE:
+            assert (cur, prev) == (100, 0)
+        else:
+            assert (cur, prev) == (run["cur"], run["prev"])
+        assert n_evals == run["n_evals"] and end_ms == run["end_ms"]
+    # and the batched call gives the same records as the loop
+    dec = api.evaluate_canaries(store).cpu().numpy()
+    for case in (c for c in cases if c["geometry"] == "irr"):
+        run = case["runs"][0]
+        assert tuple(dec[case["pair"], :5]) == (run["cur"], run["prev"], run["state"], run["n_promotions"], run["n_evals"])
