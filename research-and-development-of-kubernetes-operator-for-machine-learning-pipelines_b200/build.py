@@ -18,7 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcanarygate.so")
-HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_stream.cuh", "cg_irregular.cuh", "cg_synth.cuh",
+HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_warp.cuh", "cg_irregular.cuh", "cg_synth.cuh",
            os.path.join(ROOT, "include", "canary_gate.h")]
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -26,14 +26,14 @@ CFLAGS = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-fmad=false", "-Xcompiler", 
 
 
 def _units():
-    units = [("cg_api", "cg_api.cu", [])]
+    # CG_ABLATE=1: developer build with the tuning knobs (ring depth, CTAs per SM) read from the environment
+    extra = ["-DCG_ABLATE"] if os.environ.get("CG_ABLATE") else []
+    units = [("cg_api", "cg_api.cu", extra)]
     for tname, tchar in (("double", "d"), ("float", "f")):
         for nq in (1, 2, 3, 4):
-            name = f"cg_launch_stream_{tchar}{nq}"
+            name = f"cg_launch_warp_{tchar}{nq}"
             defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]
-            if os.environ.get("CG_TIMING") and name == "cg_launch_stream_d1":
-                defs += ["-DCG_TIMING", "-DCG_TIMING_EXPORT"]    # developer aid: in-kernel phase timers (tools/profile_kernel.py)
-            units.append((name, "cg_stream_inst.cu", defs))
+            units.append((name, "cg_warp_inst.cu", defs))
     return units
 
 

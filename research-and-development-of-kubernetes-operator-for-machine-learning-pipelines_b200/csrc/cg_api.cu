@@ -10,7 +10,7 @@
 
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
-#include "cg_stream.cuh"
+#include "cg_warp.cuh"
 #include "cg_irregular.cuh"
 #include "cg_synth.cuh"
 
@@ -122,90 +122,83 @@ int launch_general(const GeneralPlan& plan, cudaStream_t s) {
     return CG_OK;
 }
 
-// ---- streaming kernel: eligibility, shared-memory plan, launch ----------------------
+// ---- streaming kernel (cg_warp.cuh): eligibility, shared-memory plan, launch -----------
 struct StreamPlan {
-    cg::StreamArgs args;
-    int grid, block, cw_template;
+    cg::WarpArgs args;
+    int grid;
 };
 
-// doubles per thread of the streaming kernel's shared-memory record (cg::Rec<NQ>::kDoubles)
-int rec_doubles(int n_q) {
-    switch (n_q <= 1 ? 1 : n_q) {
-        case 1: return cg::Rec<1>::kDoubles;
-        case 2: return cg::Rec<2>::kDoubles;
-        case 3: return cg::Rec<3>::kDoubles;
-        default: return cg::Rec<4>::kDoubles;
-    }
+constexpr size_t kWarpState = (size_t)cg::kFields * cg::kLaneTicks * 32 * 8;   // per-tick state arrays
+constexpr size_t kWarpScratch = (size_t)2 * cg::kLaneWin * 32 * 8;             // window values + thresholds
+
+size_t warp_fixed_smem(const cg_params* p) {
+    const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
+    const size_t uses = 2 * (((size_t)p->n_scalar + cg::kRowsPerUse - 1) / cg::kRowsPerUse) +
+                        (p->n_buckets > 0 ? 2 * (1 + ((size_t)p->n_buckets - 1 + cg::kRowsPerUse - 1) / cg::kRowsPerUse) : 0);
+    return kWarpState + kWarpScratch + 2 * sizeof(cg::SlotGeom) + 2 * n_words * 4 + uses * sizeof(cg::FillEntry) +
+           8 * 16 + 64;
 }
 
 bool stream_eligible(const cg_params* p) {
     if ((int64_t)p->window_ms != 4 * (int64_t)p->period_ms) return false;
     if (3 * (int64_t)p->tick_step_ms != 2 * (int64_t)p->period_ms) return false;
-    if (p->n_scalar + p->n_buckets == 0 || p->n_ticks < 1) return false;
+    if (p->n_ticks < 1 || p->n_ticks > 16384) return false;
     if (p->n_buckets > 64 || p->n_scalar < 1) return false;   // exact fallback holds two buckets per lane; ratios come from the scalar rows
-    if (p->n_samples < 4) return false;
-    const int groups = (p->n_ticks + cg::kG - 1) / cg::kG;
-    if (groups > 15 * 32) return false;
-    const size_t slot = (size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p);
+    if (p->n_samples < cg::kTile) return false;               // a lane's 12-sample tile must fit the series
+    const size_t slot = (size_t)cg::kRowsPerUse * p->row_pitch * elem_size(p);
     if (slot >= (1u << 20)) return false;
     // 32-bit time arithmetic in the kernel
     if ((int64_t)p->tick0_ms + (int64_t)p->n_ticks * p->tick_step_ms >= (1ll << 30)) return false;
     if ((int64_t)p->n_samples * p->period_ms >= (1ll << 30) || p->tick0_ms < -(1 << 30)) return false;
-    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * (((size_t)p->n_ticks + 31) / 32) * 4 + 2 * 32 * 8 + 256 +
-                         (size_t)((groups + 31) / 32) * 32 * rec_doubles(p->n_q) * 8;
-    return 3 * slot + fixed <= (size_t)kMaxSmem;
+    // all scalar rows of a version are resident at once; one more slot keeps the stream going
+    const size_t need = ((size_t)p->n_scalar + cg::kRowsPerUse - 1) / cg::kRowsPerUse + 1;
+    return (need < 2 ? 2 : need) * slot + warp_fixed_smem(p) <= (size_t)kMaxSmem;
 }
 
 int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
-    cg::StreamArgs& a = plan->args;
+    cg::WarpArgs& a = plan->args;
     memset(&a, 0, sizeof(a));
     a.p = *p;
     a.n_pairs = n_pairs;
-    a.n_groups = (p->n_ticks + cg::kG - 1) / cg::kG;
-    a.consumer_warps = (a.n_groups + 31) / 32;
-    plan->cw_template = a.consumer_warps <= 4 ? 4 : 15;
-    a.slot_bytes = (uint32_t)((size_t)cg::kRowsPerSlot * p->row_pitch * elem_size(p));
+    a.row_bytes = (uint32_t)((size_t)p->row_pitch * elem_size(p));
+    a.slot_bytes = (uint32_t)cg::kRowsPerUse * a.row_bytes;
+    cg::fill_warp_constants(a);
     const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
-    a.range_s = (double)p->window_ms / 1000.0;
-    a.rc_range = 1.0 / a.range_s;
-    a.sampled = (double)(3 * (int64_t)p->period_ms) / 1000.0;
-    a.rc_sampled = 1.0 / a.sampled;
-    {
-        const double avg = a.sampled / 3.0;     // sampled / (n - 1), n = 4
-        a.thr = avg * 1.1;
-        a.half_avg = avg / 2;
-    }
-    a.rec_doubles = rec_doubles(p->n_q);
-    const size_t rec = (size_t)a.consumer_warps * 32 * a.rec_doubles * 8;
-    const size_t fixed = (size_t)p->n_buckets * 8 + 3 * n_words * 4 + 2 * 32 * 8 + 256 + rec;
+    const size_t fixed = warp_fixed_smem(p);
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    // as many CTAs per SM as still leave each a ring of >= 6 slots (fewer only if forced)
-    const int threads = a.consumer_warps * 32;
-    int per_sm = 1, slots = 0;
-    int c_max = a.consumer_warps <= 4 ? 4 : 1;
-    if (const char* e = getenv("CG_STREAM_PER_SM")) { int v = atoi(e); if (v >= 1 && v < c_max) c_max = v; }   // tuning aid
-    for (int c = c_max; c >= 1; --c) {
-        if (c * threads > 2048) continue;
-        const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
-        if (budget <= fixed) continue;
-        const int sl = (int)((budget - fixed) / a.slot_bytes);
-        if (sl >= 3) { per_sm = c; slots = sl; break; }
-        if (sl >= 3 && slots == 0) { per_sm = c; slots = sl; }
-    }
-    if (slots < 3) return fail(CG_EINVAL, "streaming kernel: ring does not fit shared memory");
-    if (slots > 32) slots = 32;
-    if (const char* e = getenv("CG_STREAM_SLOTS")) { int v = atoi(e); if (v >= 3 && v < slots) slots = v; }   // tuning aid
+    // one warp per CTA: as many CTAs per SM as still leave each a ring of >= 4 slots (fewer if forced)
+    int per_sm = 0, slots = 0;
+    const int floor_slots = a.n_sc_uses + 1 > 2 ? a.n_sc_uses + 1 : 2;     // scalar rows of a version are resident together
+    int c_max = 8, want = floor_slots > 4 ? floor_slots : 4;
+#ifdef CG_ABLATE
+    if (const char* e = getenv("CG_WARP_PER_SM")) { int v = atoi(e); if (v >= 1 && v <= 16) c_max = v; }
+    if (const char* e = getenv("CG_WARP_SLOTS")) { int v = atoi(e); if (v >= 2 && v <= 16) want = v; }
+#endif
+    for (int need = want; need >= floor_slots && !per_sm; --need)
+        for (int c = c_max; c >= 1; --c) {
+            const size_t budget = (size_t)(kMaxSmem + 1024) / c - 1024;
+            if (budget <= fixed) continue;
+            const int sl = (int)((budget - fixed) / a.slot_bytes);
+            if (sl >= need) { per_sm = c; slots = sl; break; }
+        }
+    if (!per_sm) return fail(CG_EINVAL, "streaming kernel: ring does not fit shared memory");
+    if (slots > 8 && slots > floor_slots) slots = floor_slots > 8 ? floor_slots : 8;
+#ifdef CG_ABLATE
+    if (const char* e = getenv("CG_WARP_SLOTS")) { int v = atoi(e); if (v >= floor_slots && v < slots) slots = v; }
+#endif
     a.n_slots = slots;
-    size_t off = (size_t)slots * a.slot_bytes;
-    a.off_le = (uint32_t)off;   off += (size_t)p->n_buckets * 8;
-    a.off_bits = (uint32_t)off; off += 3 * n_words * 4 + 16;
-    off = (off + 7) & ~(size_t)7;
-    a.off_bars = (uint32_t)off; off += (size_t)slots * 8 + (size_t)slots * 4 + 8;
+    size_t off = (size_t)slots * a.slot_bytes;          // the ring sits at offset 0
+    a.off_bars = (uint32_t)off;    off += (size_t)slots * 8;
     off = (off + 15) & ~(size_t)15;
-    a.off_rec = (uint32_t)off; off += rec;
+    a.off_state = (uint32_t)off;   off += kWarpState;
+    a.off_scratch = (uint32_t)off; off += kWarpScratch;
+    a.off_geom = (uint32_t)off;    off += 2 * sizeof(cg::SlotGeom);
+    a.off_bits = (uint32_t)off;    off += 2 * n_words * 4;
+    off = (off + 7) & ~(size_t)7;
+    a.off_tab = (uint32_t)off;     off += (size_t)a.uses_per_pass * sizeof(cg::FillEntry);
+    off = (off + 15) & ~(size_t)15;
     a.smem_bytes = (uint32_t)off;
-    plan->block = threads;
     int64_t g = (int64_t)sms * per_sm;
     if (g > n_pairs) g = n_pairs;
     if (g < 1) g = 1;
@@ -214,22 +207,21 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
 }
 
 }  // namespace
-// one per translation unit cg_stream_inst.cu (see build.py)
-#define CG_DECL_INST(n) cudaError_t n(const cg::StreamArgs&, int, int, int, cudaStream_t)
-CG_DECL_INST(cg_launch_stream_d1); CG_DECL_INST(cg_launch_stream_d2); CG_DECL_INST(cg_launch_stream_d3);
-CG_DECL_INST(cg_launch_stream_d4); CG_DECL_INST(cg_launch_stream_f1); CG_DECL_INST(cg_launch_stream_f2);
-CG_DECL_INST(cg_launch_stream_f3); CG_DECL_INST(cg_launch_stream_f4);
+// one per translation unit cg_warp_inst.cu (see build.py)
+#define CG_DECL_INST(n) cudaError_t n(const cg::WarpArgs&, int, cudaStream_t)
+CG_DECL_INST(cg_launch_warp_d1); CG_DECL_INST(cg_launch_warp_d2); CG_DECL_INST(cg_launch_warp_d3);
+CG_DECL_INST(cg_launch_warp_d4); CG_DECL_INST(cg_launch_warp_f1); CG_DECL_INST(cg_launch_warp_f2);
+CG_DECL_INST(cg_launch_warp_f3); CG_DECL_INST(cg_launch_warp_f4);
 namespace {
 
 int launch_stream(const StreamPlan& plan, cudaStream_t s) {
-    typedef cudaError_t (*fn_t)(const cg::StreamArgs&, int, int, int, cudaStream_t);
+    typedef cudaError_t (*fn_t)(const cg::WarpArgs&, int, cudaStream_t);
     static const fn_t table[2][4] = {
-        {cg_launch_stream_d1, cg_launch_stream_d2, cg_launch_stream_d3, cg_launch_stream_d4},
-        {cg_launch_stream_f1, cg_launch_stream_f2, cg_launch_stream_f3, cg_launch_stream_f4}};
+        {cg_launch_warp_d1, cg_launch_warp_d2, cg_launch_warp_d3, cg_launch_warp_d4},
+        {cg_launch_warp_f1, cg_launch_warp_f2, cg_launch_warp_f3, cg_launch_warp_f4}};
     int nq = plan.args.p.n_q < 1 ? 1 : plan.args.p.n_q;
-    const cudaError_t e = table[plan.args.p.dtype == CG_F32 ? 1 : 0][nq - 1](plan.args, plan.grid, plan.block,
-                                                                           plan.cw_template, s);
-    if (e != cudaSuccess) return cuda_fail(e, "launch stream_kernel");
+    const cudaError_t e = table[plan.args.p.dtype == CG_F32 ? 1 : 0][nq - 1](plan.args, plan.grid, s);
+    if (e != cudaSuccess) return cuda_fail(e, "launch warp_kernel");
     g_launches.fetch_add(1);
     return CG_OK;
 }
@@ -285,7 +277,7 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     if ((decisions || p->n_ticks >= 32) && path != 1 && stream_eligible(p)) {
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
-        cg::StreamArgs& a = sp.args;
+        cg::WarpArgs& a = sp.args;
         a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
         a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
         a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
@@ -524,7 +516,7 @@ int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* 
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
         if (grid) *grid = sp.grid;
-        if (block) *block = sp.block;
+        if (block) *block = 32;
         if (smem_bytes) *smem_bytes = (int32_t)sp.args.smem_bytes;
         return CG_OK;
     }

@@ -8,11 +8,31 @@
 #pragma once
 #include <stdint.h>
 #include <math.h>
+#include <string.h>
 #include "../../include/canary_gate.h"
 
-namespace cg {
-
+// The per-lane arithmetic (this file and cg_warp.cuh's lane functions) also compiles as plain
+// C++ so that tests/host_emul can run it against the oracle without a GPU.  That build is test
+// infrastructure; the product is the sm_100a build.
+#ifdef __CUDACC__
 #define CG_DEVINL __device__ __forceinline__
+#define CG_DEVNOINL static __device__ __noinline__
+#define CG_DEVMEM __device__ __forceinline__
+#else
+#include <cmath>
+#define CG_DEVINL static inline
+#define CG_DEVNOINL static __attribute__((noinline))
+#define CG_DEVMEM inline
+using std::isinf;
+using std::isnan;
+static inline int __ffs(unsigned x) { return x ? __builtin_ctz(x) + 1 : 0; }
+static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned sh) {
+    sh &= 31u;
+    return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
+}
+#endif
+
+namespace cg {
 
 CG_DEVINL int64_t floor_div(int64_t a, int64_t b) {
     int64_t q = a / b, r = a % b;
@@ -55,23 +75,67 @@ CG_DEVINL TickGeom tick_geom(const cg_params& p, int32_t phase, int tick) {
     return g;
 }
 
+// high word of a double (sign, exponent, top of the significand)
+CG_DEVINL uint32_t hi_word(double v) {
+#ifdef __CUDACC__
+    return (uint32_t)__double2hiint(v);
+#else
+    uint64_t u;
+    memcpy(&u, &v, 8);
+    return (uint32_t)(u >> 32);
+#endif
+}
+// biased exponent in [lo, lo + span): one integer subtract and compare (false for 0, denormals, Inf, NaN
+// when lo >= 1 and lo + span <= 2047)
+CG_DEVINL bool exp_in(double v, uint32_t lo, uint32_t span) { return ((hi_word(v) >> 20) & 0x7ffu) - lo < span; }
+
+// Out-of-line IEEE division: one copy of the generic routine (with its special-case path) instead
+// of one per use.
+CG_DEVNOINL double ddiv_call(double a, double b) { return a / b; }
+
 // a / c for a constant c with rc = 1/c correctly rounded: the Markstein sequence
 // (q = a*rc; r = fma(-q, c, a); q + r*rc) gives the correctly rounded quotient, i.e. exactly what
-// IEEE division gives, in three operations instead of the ~120-cycle division routine.  Checked
+// IEEE division gives, in three operations instead of the ~45-instruction division routine.  Checked
 // against true division on 2e8 random doubles over 80 binades and every integer in [-3e5, 4e6]
 // for each constant used here (tests/test_div_const.py keeps a smaller version of that check).
-// Magnitudes near the overflow / underflow ends take the true division.
-// Out-of-line IEEE division: one copy of the ~40-instruction sequence instead of one per use in
-// code that runs once per (pair, version) and has to stay small for the instruction cache.
-static __device__ __noinline__ double ddiv_call(double a, double b) { return a / b; }
-
+// c is within a few binades of 1 here (1000, the window and sample spans in seconds).  Zero goes
+// straight through; magnitudes near the overflow / underflow ends, Inf and NaN take the true division.
 CG_DEVINL double div_const(double a, double c, double rc) {
     const double q = a * rc;
     const double r = fma(-q, c, a);
     const double q2 = fma(r, rc, q);
-    const double aa = fabs(a);
-    if (!(aa < 1e300 && (aa > 1e-290 || a == 0.0))) return ddiv_call(a, c);
-    return q2;
+    if (exp_in(a, 60u, 1960u)) return q2;          // 2^-963 <= |a| < 2^997
+    if (a == 0.0) return q2;                        // +-0 / c = +-0 = q2
+    return ddiv_call(a, c);
+}
+
+// a / b for b > 0, both in a safe range: float reciprocal seed, two Newton steps, Markstein
+// quotient with two residual corrections.  The value before the last rounding is within about
+// 2^-54 ulp of a/b, and a quotient of doubles stays at least 2^-53/m ulp away from a rounding
+// boundary (m in [1,2) the divisor's significand), so the rounding can only go wrong for
+// significands next to 2 (4 / 0x1.fffffffffffffp+4 does): divisors whose top 20 fraction bits are
+// all ones take the true division, as does anything outside the exponent range.
+// tests/test_div_const.py checks it against IEEE division on random and adversarial operands.
+CG_DEVINL double ddiv_pos(double a, double b) {
+    if (exp_in(b, 923u, 200u) && exp_in(a, 223u, 1600u) &&     // 2^-100 <= b < 2^100, 2^-800 <= |a| < 2^800
+        (hi_word(b) & 0xfffffu) != 0xfffffu) {
+#ifdef __CUDACC__
+        double y = (double)__frcp_rn((float)b);
+#else
+        double y = (double)(1.0f / (float)b);
+#endif
+        double e = fma(-b, y, 1.0);
+        y = fma(y, e, y);
+        e = fma(-b, y, 1.0);
+        y = fma(y, e, y);
+        double q = a * y;
+        double r = fma(-b, q, a);
+        q = fma(r, y, q);
+        r = fma(-b, q, a);
+        return fma(r, y, q);
+    }
+    if (a == 0.0 && exp_in(b, 1u, 2046u)) return a;            // +-0 / (finite b > 0) = +-0
+    return ddiv_call(a, b);
 }
 
 // Same as tick_geom with 32-bit integer arithmetic, for callers that have checked that every

@@ -1,0 +1,9 @@
+// cg_warp_inst.cu -- one translation unit per (element type, quantile count) instance of the
+// streaming kernel, so the instances compile in parallel.  Built with
+//   -DCG_INST_T=double|float -DCG_INST_NQ=1..4 -DCG_INST_NAME=cg_launch_warp_<d|f><nq>
+#include <cuda_runtime.h>
+#include "cg_warp.cuh"
+
+cudaError_t CG_INST_NAME(const cg::WarpArgs& a, int grid, cudaStream_t s) {
+    return cg::launch_warp_tn<CG_INST_T, CG_INST_NQ>(a, grid, s);
+}

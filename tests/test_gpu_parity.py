@@ -119,13 +119,17 @@ CONFIGS = {
     "odd_tick0": dict(make=dict(n_samples=100, n_buckets=8, tick0_ms=75000), n=24, gen={}),
     "late_tick0_many_ticks": dict(make=dict(n_samples=240, n_buckets=6, tick0_ms=45000, n_ticks=400), n=10, gen={}),
     "q_edges": dict(make=dict(n_samples=60, n_buckets=8, quantiles=(0.0, 1.0, -0.5, 1.5), gate_q=1), n=16, gen={}),
+    "two_passes_800_ticks": dict(make=dict(n_samples=600, n_buckets=5, n_ticks=800), n=6, gen=dict(adversarial=0.2)),
+    "twelve_samples": dict(make=dict(n_samples=12, n_buckets=4, n_ticks=14), n=17, gen={}),
+    "k1_b3_tiny_grid": dict(make=dict(n_samples=40, n_scalar=1, n_buckets=3, roles=[3], n_ticks=5), n=300, gen={}),
 }
 
 
-# geometries the streaming kernel covers (window = 4 periods, tick step = 2/3 period)
+# geometries the streaming kernel covers (window = 4 periods, tick step = 2/3 period, >= 12 samples)
 STREAMING = {"cfg2_error_rate_only", "cfg3_quantiles", "cfg4_full_resets", "k5_feedback_b12",
-             "left_open_coincident", "closed_coincident", "ragged_pitch", "short_series",
-             "single_bucket", "two_buckets", "k16_b64", "odd_tick0", "late_tick0_many_ticks", "q_edges"}
+             "left_open_coincident", "closed_coincident", "ragged_pitch",
+             "single_bucket", "two_buckets", "k16_b64", "odd_tick0", "late_tick0_many_ticks", "q_edges",
+             "two_passes_800_ticks", "twelve_samples", "k1_b3_tiny_grid"}
 
 
 @pytest.mark.parametrize("name", sorted(CONFIGS))
@@ -182,10 +186,10 @@ def test_empty_batch_is_a_no_op():
 
 
 def test_oversized_geometry_is_rejected_cleanly():
-    p = P.make_params(n_samples=4096, n_buckets=64)
+    p = P.make_params(n_samples=16384, n_buckets=64)     # one row = 128 KB: no ring, no resident tile
     z = lambda *s, dt=torch.float64: torch.zeros(s, dtype=dt, device="cuda")  # noqa: E731
     with pytest.raises(RuntimeError, match="shared memory"):
-        engine.eval_fused(z(1, 2, 4, 4096), z(1, 2, 64, 4096), z(64), z(1, 2, dt=torch.int32), p)
+        engine.eval_fused(z(1, 2, 4, 16384), z(1, 2, 64, 16384), z(64), z(1, 2, dt=torch.int32), p)
 
 
 def test_cpu_tensors_are_refused():

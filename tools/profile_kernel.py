@@ -13,7 +13,6 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 path = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 p = P.make_params()
-p.reserved = int(os.environ.get('CG_DEBUG', '0'))
 le = torch.from_numpy(synth.default_le(p.n_buckets)).cuda()
 sc, bk, ph = engine.synth_fill(n, p, le, seed=0xC0FFEE + 3)
 torch.cuda.synchronize()
@@ -27,13 +26,3 @@ ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(reps)]
 gb = n * p.bytes_per_pair() / 1e9
 print(f"pairs={n} path={path} ms={['%.3f' % m for m in ms]} GB/s={gb / (min(ms) * 1e-3):.1f} states={torch.bincount(dec[:, 2], minlength=4).tolist()}")
 
-if os.environ.get("CG_TIMING"):
-    import ctypes as C
-    from canary_b200 import _lib
-    buf = (C.c_ulonglong * 16)()
-    _lib.lib.cg_debug_timing(buf, 1)
-    names = ["wait_full", "rows", "setup", "finish", "barrier", "total", "warps", "coop_calls", "finish_quantile", "finish_fallback", "-", "-", "-", "-", "-", "-"]
-    ti = 5
-    vals = list(buf)
-    tot = vals[ti] or 1
-    print("warp-cycles over all launches:", {n: f"{v:.3e} ({100 * v / tot:.1f}%)" for n, v in zip(names, vals)})
