@@ -28,11 +28,13 @@ CFLAGS = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-fmad=false", "-Xcompiler", 
 def _units():
     # CG_ABLATE=1: developer build with the tuning knobs (ring depth, CTAs per SM) read from the environment
     extra = ["-DCG_ABLATE"] if os.environ.get("CG_ABLATE") else []
+    if os.environ.get("CG_G"):                       # developer build: periods of the tick grid per lane (1, 2 or 4)
+        extra += [f"-DCG_G={int(os.environ['CG_G'])}"]
     units = [("cg_api", "cg_api.cu", extra)]
     for tname, tchar in (("double", "d"), ("float", "f")):
         for nq in (1, 2, 3, 4):
             name = f"cg_launch_warp_{tchar}{nq}"
-            defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"]
+            defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"] + extra
             units.append((name, "cg_warp_inst.cu", defs))
     return units
 

@@ -128,14 +128,14 @@ struct StreamPlan {
     int grid;
 };
 
-constexpr size_t kWarpState = (size_t)cg::kFields * cg::kLaneTicks * 32 * 8;   // per-tick state arrays
-constexpr size_t kWarpScratch = (size_t)2 * cg::kLaneWin * 32 * 8;             // window values + thresholds
+constexpr size_t kWarpState = (size_t)cg::kFields * cg::kLaneTicks * cg::kLanes * 8;   // per-tick state arrays
+constexpr size_t kWarpScratch = (size_t)cg::kLaneWin * cg::kLanes * 8;                 // window thresholds
 
 size_t warp_fixed_smem(const cg_params* p) {
     const size_t n_words = ((size_t)p->n_ticks + 31) / 32;
     const size_t uses = 2 * (((size_t)p->n_scalar + cg::kRowsPerUse - 1) / cg::kRowsPerUse) +
                         (p->n_buckets > 0 ? 2 * (1 + ((size_t)p->n_buckets - 1 + cg::kRowsPerUse - 1) / cg::kRowsPerUse) : 0);
-    return kWarpState + kWarpScratch + 2 * sizeof(cg::SlotGeom) + 2 * n_words * 4 + uses * sizeof(cg::FillEntry) +
+    return kWarpState + kWarpScratch + 2 * cg::kWarps * sizeof(cg::SlotGeom) + 2 * n_words * 4 + uses * sizeof(cg::FillEntry) +
            8 * 16 + 64;
 }
 
@@ -167,10 +167,10 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     const size_t fixed = warp_fixed_smem(p);
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    // one warp per CTA: as many CTAs per SM as still leave each a ring of >= 4 slots (fewer if forced)
+    // a CTA is the kWarps warps of one pair: as many CTAs per SM as still leave each a ring of `want` slots (fewer if forced)
     int per_sm = 0, slots = 0;
     const int floor_slots = a.n_sc_uses + 1 > 2 ? a.n_sc_uses + 1 : 2;     // scalar rows of a version are resident together
-    int c_max = 8, want = floor_slots > 4 ? floor_slots : 4;
+    int c_max = cg::kG == 1 ? 4 : 8, want = floor_slots > 3 ? floor_slots : 3;
 #ifdef CG_ABLATE
     if (const char* e = getenv("CG_WARP_PER_SM")) { int v = atoi(e); if (v >= 1 && v <= 16) c_max = v; }
     if (const char* e = getenv("CG_WARP_SLOTS")) { int v = atoi(e); if (v >= 2 && v <= 16) want = v; }
@@ -193,7 +193,7 @@ int plan_stream(const cg_params* p, int64_t n_pairs, StreamPlan* plan) {
     off = (off + 15) & ~(size_t)15;
     a.off_state = (uint32_t)off;   off += kWarpState;
     a.off_scratch = (uint32_t)off; off += kWarpScratch;
-    a.off_geom = (uint32_t)off;    off += 2 * sizeof(cg::SlotGeom);
+    a.off_geom = (uint32_t)off;    off += 2 * cg::kWarps * sizeof(cg::SlotGeom);
     a.off_bits = (uint32_t)off;    off += 2 * n_words * 4;
     off = (off + 7) & ~(size_t)7;
     a.off_tab = (uint32_t)off;     off += (size_t)a.uses_per_pass * sizeof(cg::FillEntry);
@@ -516,7 +516,7 @@ int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* 
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
         if (grid) *grid = sp.grid;
-        if (block) *block = 32;
+        if (block) *block = cg::kLanes;
         if (smem_bytes) *smem_bytes = (int32_t)sp.args.smem_bytes;
         return CG_OK;
     }

@@ -43,16 +43,27 @@
 
 namespace cg {
 
-constexpr int kLaneTicks = 12;     // ticks per lane (4 periods of the tick grid)
-constexpr int kLaneWin = 9;        // window start positions per lane tile
-constexpr int kTile = 12;          // samples per lane tile
-constexpr int kChunkTicks = 382;   // ticks one pass over the rows covers (384 minus the rotation slack)
+// A lane owns kG periods of the tick grid (3 ticks and 2 new samples each).  4/kG warps share one
+// pair, so that 128 lane-periods = 384 ticks are covered in one pass whatever kG is: kG = 4 is one
+// warp with 12 ticks per lane, kG = 2 two warps with 6 ticks per lane (half the per-warp state and
+// ring, twice the resident warps).
+#ifndef CG_G
+#define CG_G 2
+#endif
+constexpr int kG = CG_G;
+static_assert(kG == 1 || kG == 2 || kG == 4, "kG must be 1, 2 or 4");
+constexpr int kWarps = 4 / kG;             // warps per pair (= per CTA)
+constexpr int kLanes = 32 * kWarps;        // lanes per pair
+constexpr int kLaneTicks = 3 * kG;         // ticks per lane
+constexpr int kLaneWin = 2 * kG + 1;       // window start positions per lane tile
+constexpr int kTile = 2 * kG + 4;          // samples per lane tile
+constexpr int kChunkTicks = 382;           // ticks one pass over the rows covers (384 minus the rotation slack)
 constexpr int kRowsPerUse = 2;     // rows per ring slot
 constexpr unsigned kFullMask = 0xffffffffu;
 
 #ifndef __CUDACC__
 // host emulation only: what a lane's last bucket row did (warp-level statistics in tests/host_emul)
-struct EmulRowStat { int reset, event, windows, captures, clamps; };
+struct EmulRowStat { int reset, event, windows, captures, clamps, cfl, hfl; };
 static EmulRowStat g_emul_row;
 #define CG_EMUL_STAT(field, v) (g_emul_row.field += (v))
 #else
@@ -63,8 +74,7 @@ static EmulRowStat g_emul_row;
 constexpr int kFA = 0;    // new version's error_rate until the old one's scalar rows are done; then observations (rate of the +Inf bucket)
 constexpr int kFB = 1;    // new version's latency_avg; then the per-tick rate-space maximum of excluded rows
 constexpr int kFSQ = 2;   // new version's gate quantile, in the NEW version's lane coordinates
-constexpr int kFQC = 3;   // gate quantile of the version being processed
-constexpr int kFields = 4;
+constexpr int kFields = 3;
 
 struct WarpArgs {
     const void*    scalars;
@@ -170,7 +180,7 @@ struct LaneGeo {
 CG_DEVINL LaneGeo lane_setup(const WarpArgs& a, const SlotGeom& g, int lane, int chunk0, int chunk_end,
                              unsigned& valid_ticks) {
     LaneGeo lg;
-    const int b = g.i00 + 8 * lane;
+    const int b = g.i00 + 2 * kG * lane;
     const int lim = (a.p.n_samples - kTile) & ~1;
     int bt = b < 0 ? 0 : b;
     if (bt > lim) bt = lim;
@@ -182,7 +192,7 @@ CG_DEVINL LaneGeo lane_setup(const WarpArgs& a, const SlotGeom& g, int lane, int
         const int c = g.off[s] + lg.dl;
         const bool n4 = g.n4[s] != 0;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
+        for (int kk = 0; kk < kG; ++kk) {
             const int tt = 3 * kk + s, j = tick_base + tt, k = 2 * kk + c;
             if (j >= chunk0 && j < chunk_end) {
                 valid_ticks |= 1u << tt;
@@ -199,13 +209,12 @@ CG_DEVINL int lane_window(const SlotGeom& g, const LaneGeo& lg, int tt) {
 
 // this lane's column of the shared-memory state
 struct Lane {
-    int lane;
+    int lane;     // lane of the pair, 0 .. kLanes-1
     double* st;   // per-tick state:  st[(field*kLaneTicks + tt)*32]
-    double* sa;   // scratch:         sa[k*32] window maxima, sa[(kLaneWin+k)*32] window thresholds
+    double* sa;   // scratch:         sa[k*32] window thresholds (after the last bucket row: the final window maxima)
 };
-#define CG_ST(L, f, tt) (L).st[((f) * kLaneTicks + (tt)) * 32]
-#define CG_SA(L, k) (L).sa[(k) * 32]
-#define CG_SY(L, k) (L).sa[(kLaneWin + (k)) * 32]
+#define CG_ST(L, f, tt) (L).st[((f) * kLaneTicks + (tt)) * kLanes]
+#define CG_SY(L, k) (L).sa[(k) * kLanes]
 
 // kernel-wide constants derived from `le` and the quantile list
 struct QuantConst {
@@ -262,20 +271,32 @@ CG_DEVINL void window_deltas(const double (&x)[kTile], double (&w)[kLaneWin]) {
 // a counter reset (Appendix A step 2) or an unordered pair (NaN) anywhere in the tile; three
 // independent compare chains, so the pipeline is not one serial run of dependent predicates
 CG_DEVINL bool tile_has_reset(const double (&x)[kTile]) {
-    const bool a = !(x[1] >= x[0]) | !(x[2] >= x[1]) | !(x[3] >= x[2]) | !(x[4] >= x[3]);
-    const bool b = !(x[5] >= x[4]) | !(x[6] >= x[5]) | !(x[7] >= x[6]) | !(x[8] >= x[7]);
-    const bool c = !(x[9] >= x[8]) | !(x[10] >= x[9]) | !(x[11] >= x[10]);
-    return a | b | c;
+    bool r[3] = {false, false, false};
+#pragma unroll
+    for (int i = 0; i + 1 < kTile; ++i) r[i % 3] |= !(x[i + 1] >= x[i]);
+    return r[0] | r[1] | r[2];
 }
 
-// the oracle's conditional adds of the value before each reset, per window, in time order
+// value before each reset (0 where there is none), added to each window in time order; adding
+// +0.0 leaves a sum unchanged, so this is the oracle's conditional add
 CG_DEVINL void fix_resets(const double (&x)[kTile], double (&w)[kLaneWin]) {
+    double d[kTile - 1];
 #pragma unroll
-    for (int k = 0; k < kLaneWin; ++k) {
-        if (x[k + 1] < x[k]) w[k] += x[k];
-        if (x[k + 2] < x[k + 1]) w[k] += x[k + 1];
-        if (x[k + 3] < x[k + 2]) w[k] += x[k + 2];
-    }
+    for (int i = 0; i + 1 < kTile; ++i) d[i] = (x[i + 1] < x[i]) ? x[i] : 0.0;
+#pragma unroll
+    for (int k = 0; k < kLaneWin; ++k) w[k] = ((w[k] + d[k]) + d[k + 1]) + d[k + 2];
+}
+
+// v[k] for a run-time k without sending the array to local memory
+CG_DEVINL double pick_window(const double (&v)[kLaneWin], int k) {
+#ifdef __CUDACC__
+    double r = v[0];
+#pragma unroll
+    for (int i = 1; i < kLaneWin; ++i) r = (k == i) ? v[i] : r;
+    return r;
+#else
+    return v[k];
+#endif
 }
 
 // Appendix A step 2 for the 4 samples at t4; also returns the first sample
@@ -317,6 +338,15 @@ CG_DEVINL double tick_increase(const WarpArgs& a, const SlotGeom& g, int s, doub
     return res * g.f[s];
 }
 
+// where the new version keeps the values of the tick that is local tick tt of this (old-version) lane
+CG_DEVINL const double* new_version_column(const Lane& L, int tt, int delta, int& tn) {
+    tn = tt + delta;
+    int ln = L.lane;
+    if (tn < 0) { tn += kLaneTicks; --ln; }
+    if (tn >= kLaneTicks) { tn -= kLaneTicks; ++ln; }
+    return (ln >= 0 && ln < kLanes) ? L.st + (ln - L.lane) : nullptr;
+}
+
 // ---- scalar rows: sum(increase(...)) per role and tick (:375-410), then the derived metrics
 // (:387-404).  All K scalar rows of the version are resident (row_ptr(r) -> row r in the ring), so
 // the loop is tick-outer and needs five running sums, not sixty.
@@ -331,51 +361,72 @@ CG_DEVINL void scalar_phase(const WarpArgs& a, const SlotGeom& g, const LaneGeo&
     const cg_params& p = a.p;
     const int K = p.n_scalar, W = p.n_q + CG_M_EXTRA;
     const bool need_e = (p.checks & CG_G_ERR_OK) != 0, need_a = (p.checks & CG_G_AVG_OK) != 0;
+    unsigned have = 0u;
+    for (int r = 0; r < K; ++r) have |= p.scalar_role[r];
 #pragma unroll 1
-    for (int tt = 0; tt < kLaneTicks; ++tt) {
-        if (!((lg.act >> tt) & 1u)) continue;
-        const int s = tt % 3, off = lg.bt + lane_window(g, lg, tt);
-        double sums[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-        unsigned have = 0u;
+    for (int kk = 0; kk < kG; ++kk) {
 #pragma unroll 1
-        for (int r = 0; r < K; ++r) {
-            double first;
-            const double res = window4<T>(row_ptr(r) + off, first);
-            const double inc = tick_increase(a, g, s, res, first);
-            const unsigned role = p.scalar_role[r];
+        for (int s = 0; s < 3; ++s) {
+            const int tt = 3 * kk + s;
+            if (!((lg.act >> tt) & 1u)) continue;
+            const int off = lg.bt + 2 * kk + g.off[s] + lg.dl;
+            // a sum seeded with -0.0 equals "the first term, then + each further term" bit for bit
+            double sums[5] = {-0.0, -0.0, -0.0, -0.0, -0.0};
+#pragma unroll 1
+            for (int r = 0; r < K; ++r) {
+                double first;
+                const double res = window4<T>(row_ptr(r) + off, first);
+                const double inc = tick_increase(a, g, s, res, first);
+                const unsigned role = p.scalar_role[r];
+#pragma unroll
+                for (int q = 0; q < 5; ++q)
+                    if (role & (1u << q)) sums[q] += inc;
+            }
 #pragma unroll
             for (int q = 0; q < 5; ++q)
-                if (role & (1u << q)) sums[q] = (have & (1u << q)) ? sums[q] + inc : inc;
-            have |= role;
-        }
-        const double total = sums[0], err = sums[1], lsum = sums[2], lcnt = sums[3];
-        double er = NAN, avg = NAN;
-        if (total > 0) er = ddiv_pos(err, total);
-        if (lcnt > 0) avg = ddiv_pos(lsum, lcnt);
-        if (ver == 0) {
-            CG_ST(L, kFA, tt) = er;
-            CG_ST(L, kFB, tt) = avg;
-        } else {
-            int tn = tt + delta, ln = L.lane;
-            if (tn < 0) { tn += kLaneTicks; --ln; }
-            if (tn >= kLaneTicks) { tn -= kLaneTicks; ++ln; }
-            if (ln >= 0 && ln < 32) {
-                const double* o = L.st + (ln - L.lane);
-                const double er_n = o[(kFA * kLaneTicks + tn) * 32], avg_n = o[(kFB * kLaneTicks + tn) * 32];
-                const bool ok = (!need_e || er_n <= er * p.one_plus_thr[1]) &&      // :447
-                                (!need_a || avg_n <= avg * p.one_plus_thr[2]);      // :454
-                if (ok) pass_bits |= 1u << tt;
+                if (!(have & (1u << q))) sums[q] = 0.0;            // `or on() vector(0)` / no series with that role
+            const double total = sums[0], err = sums[1], lsum = sums[2], lcnt = sums[3];
+            double er = NAN, avg = NAN;
+            if (total > 0) er = ddiv_pos(err, total);
+            if (lcnt > 0) avg = ddiv_pos(lsum, lcnt);
+            if (ver == 0) {
+                CG_ST(L, kFA, tt) = er;
+                CG_ST(L, kFB, tt) = avg;
+            } else {
+                int tn;
+                const double* o = new_version_column(L, tt, delta, tn);
+                if (o) {
+                    const double er_n = o[(kFA * kLaneTicks + tn) * kLanes], avg_n = o[(kFB * kLaneTicks + tn) * kLanes];
+                    const bool ok = (!need_e || er_n <= er * p.one_plus_thr[1]) &&      // :447
+                                    (!need_a || avg_n <= avg * p.one_plus_thr[2]);      // :454
+                    if (ok) pass_bits |= 1u << tt;
+                }
             }
+            if (a.metrics) {
+                double* o = a.metrics + ((size_t)pv * p.n_ticks + tick_base + tt) * W + p.n_q;
+                o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
+                o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[4];
+            }
+            if (a.valid)
+                a.valid[(size_t)pv * p.n_ticks + tick_base + tt] =
+                    (uint8_t)((p.n_buckets > 0 ? CG_V_QUANTILE : 0) | (total > 0 ? CG_V_ERROR_RATE : 0) |
+                              (lcnt > 0 ? CG_V_LATENCY_AVG : 0));
         }
-        if (a.metrics) {
-            double* o = a.metrics + ((size_t)pv * p.n_ticks + tick_base + tt) * W + p.n_q;
-            o[CG_M_ERROR_RESPONSES] = err; o[CG_M_ERROR_RATE] = er; o[CG_M_LATENCY_AVG] = avg;
-            o[CG_M_REQUEST_COUNT] = lcnt; o[CG_M_FEEDBACK_COUNT] = sums[4];
-        }
-        if (a.valid)
-            a.valid[(size_t)pv * p.n_ticks + tick_base + tt] =
-                (uint8_t)((p.n_buckets > 0 ? CG_V_QUANTILE : 0) | (total > 0 ? CG_V_ERROR_RATE : 0) |
-                          (lcnt > 0 ? CG_V_LATENCY_AVG : 0));
+    }
+}
+
+// The gate quantile of a tick is known (captured, or the default when no bucket reaches the rank).
+// New version: it waits in the state array.  Old version: the quantile part of the gate (:440) is
+// decided on the spot against the new version's value of the same tick.
+CG_DEVINL void gate_quantile_known(const WarpArgs& a, const Lane& L, int ver, int tt, int delta, double r,
+                                   unsigned& pass_bits) {
+    if (ver == 0) {
+        CG_ST(L, kFSQ, tt) = r;
+    } else {
+        int tn;
+        const double* o = new_version_column(L, tt, delta, tn);
+        const bool ok = o && o[(kFSQ * kLaneTicks + tn) * kLanes] <= r * a.p.one_plus_thr[0];
+        pass_bits = ok ? pass_bits | (1u << tt) : pass_bits & ~(1u << tt);
     }
 }
 
@@ -383,37 +434,41 @@ CG_DEVINL void scalar_phase(const WarpArgs& a, const SlotGeom& g, const LaneGeo&
 // Speculates that the +Inf bucket holds the observations (checked in bucket_finish).
 template <typename T, int NQ>
 CG_DEVINL void inf_row_setup(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                             const QuantConst& qc, const T* __restrict__ tile, int64_t pv, int tick_base,
-                             uint64_t& found, unsigned& fb) {
+                             const QuantConst& qc, const T* __restrict__ tile, int ver, int delta, int64_t pv,
+                             int tick_base, uint64_t& found, unsigned& fb, unsigned& pass_bits) {
     const cg_params& p = a.p;
     const int W = p.n_q + CG_M_EXTRA;
 #pragma unroll
     for (int k = 0; k < kLaneWin; ++k) CG_SY(L, k) = INFINITY;
     found = ~0ull;
 #pragma unroll 1
-    for (int tt = 0; tt < kLaneTicks; ++tt) {
-        if (!((lg.act >> tt) & 1u)) continue;
-        const int s = tt % 3, k = lane_window(g, lg, tt);
-        double x0;
-        const double wv = window4<T>(tile + k, x0);
-        double obs = NAN;
-        if (finite_d(wv) && finite_d(x0)) obs = div_const(tick_increase(a, g, s, wv, x0), a.range_s, a.rc_range);
-        if (!finite_d(obs)) { fb |= 1u << tt; lg.act &= ~(1u << tt); continue; }
-        CG_ST(L, kFA, tt) = obs;
-        CG_ST(L, kFB, tt) = -INFINITY;
-        double y = CG_SY(L, k);
+    for (int kk = 0; kk < kG; ++kk) {
+#pragma unroll 1
+        for (int s = 0; s < 3; ++s) {
+            const int tt = 3 * kk + s;
+            if (!((lg.act >> tt) & 1u)) continue;
+            const int k = 2 * kk + g.off[s] + lg.dl;
+            double x0;
+            const double wv = window4<T>(tile + k, x0);
+            double obs = NAN;
+            if (finite_d(wv) && finite_d(x0)) obs = div_const(tick_increase(a, g, s, wv, x0), a.range_s, a.rc_range);
+            if (!finite_d(obs)) { fb |= 1u << tt; lg.act &= ~(1u << tt); continue; }
+            CG_ST(L, kFA, tt) = obs;
+            CG_ST(L, kFB, tt) = -INFINITY;
+            double y = CG_SY(L, k);
 #pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-            const bool searching = qc.search[q] && obs != 0;                      // Appendix A step 4
-            const double def = qc.search[q] ? (obs != 0 ? qc.le_top : NAN) : qc.qdef[q];   // step 6: no bucket reaches the rank
-            if (q == p.gate_q) CG_ST(L, kFQC, tt) = def;
-            if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick_base + tt) * W + q] = def;
-            if (searching) {
-                found &= ~(1ull << (tt * NQ + q));
-                y = fmin(y, win_threshold(p.q[q] * obs, g.rinv[s]));               // step 5
+            for (int q = 0; q < NQ; ++q) {
+                const bool searching = qc.search[q] && obs != 0;                      // Appendix A step 4
+                const double def = qc.search[q] ? (obs != 0 ? qc.le_top : NAN) : qc.qdef[q];   // step 6: no bucket reaches the rank
+                if (q == p.gate_q) gate_quantile_known(a, L, ver, tt, delta, def, pass_bits);
+                if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick_base + tt) * W + q] = def;
+                if (searching) {
+                    found &= ~(1ull << (tt * NQ + q));
+                    y = fmin(y, win_threshold(p.q[q] * obs, g.rinv[s]));               // step 5
+                }
             }
+            CG_SY(L, k) = y;
         }
-        CG_SY(L, k) = y;
     }
 }
 
@@ -426,14 +481,15 @@ CG_DEVNOINL double interpolate_quantile(const double* __restrict__ le, int b, do
 }
 
 // ---- bucket rows: the event loop --------------------------------------------------------------
-// Exact, per tick and in rate space, for the flagged windows of bucket row b.  The caller has left
-// the windows' running maxima (before this row) in the scratch column.  Returns the windows that
-// must be kept out of the running maximum for this row (a clamped tick: its value went into the
-// per-tick maximum instead).
+// Exact, per tick and in rate space, for the flagged windows of bucket row b.  prevw holds the
+// windows' running maxima before this row.  Returns the windows that must be kept out of the
+// running maximum for this row (a clamped tick: the row's values went into the per-tick maxima
+// instead).
 template <typename T, int NQ>
 CG_DEVINL unsigned bucket_events(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                                 const T* __restrict__ tile, int b, unsigned mask, int64_t pv, int tick_base,
-                                 uint64_t& found, unsigned& fb) {
+                                 const T* __restrict__ tile, int b, unsigned mask, const double (&prevw)[kLaneWin],
+                                 int ver, int delta, int64_t pv, int tick_base, uint64_t& found, unsigned& fb,
+                                 unsigned& pass_bits) {
     const cg_params& p = a.p;
     const int W = p.n_q + CG_M_EXTRA;
     unsigned excl = 0u;
@@ -445,53 +501,59 @@ CG_DEVINL unsigned bucket_events(const WarpArgs& a, const SlotGeom& g, LaneGeo& 
         double x0;
         const double res = window4<T>(tile + k, x0);
         const bool fin = finite_d(res) && finite_d(x0);
-        bool clamped = false;
-        int tts[3];
-        double cval[3];
-#pragma unroll
+        unsigned hosted = 0u, clamped = 0u;
+        double y = INFINITY;
+#pragma unroll 1
         for (int s = 0; s < 3; ++s) {
-            tts[s] = -1;
-            cval[s] = 0.0;
             const int num = k - lg.dl - g.off[s];
-            if ((num & ~6) != 0) continue;                        // num in {0, 2, 4, 6}: the window hosts a tick of slot s
+            if ((num & ~(2 * (kG - 1))) != 0) continue;           // num in {0, 2, .., 2(kG-1)}: the window hosts a tick of slot s
             const int tt = 3 * (num >> 1) + s;
             if (!((lg.act >> tt) & 1u)) continue;
             if (!fin) { fb |= 1u << tt; lg.act &= ~(1u << tt); continue; }
-            tts[s] = tt;
-            const double std_inc = res * g.f[s];
-            double inc = std_inc;
+            hosted |= 1u << s;
+            const double fs = g.f[s];
+            double inc = res * fs;
             if (!(x0 * g.gchk[s] >= res)) {
-                inc = exact_increase(res, x0, g.dstart[s], g.endt[s], a.sampled, a.rc_sampled, a.thr, a.half_avg);
-                clamped |= inc != std_inc;
+                const double e = exact_increase(res, x0, g.dstart[s], g.endt[s], a.sampled, a.rc_sampled, a.thr, a.half_avg);
+                if (e != inc) { clamped |= 1u << s; inc = e; }
             }
-            cval[s] = div_const(inc, a.range_s, a.rc_range);
-        }
-        double y = INFINITY;
-#pragma unroll
-        for (int s = 0; s < 3; ++s) {
-            const int tt = tts[s];
-            if (tt < 0) continue;
+            const double c = div_const(inc, a.range_s, a.rc_range);
             const double obs = CG_ST(L, kFA, tt);
 #pragma unroll
             for (int q = 0; q < NQ; ++q) {
                 const uint64_t bit = 1ull << (tt * NQ + q);
                 if (found & bit) continue;
                 const double rank = p.q[q] * obs;                 // step 5
-                if (cval[s] >= rank) {                            // first bucket reaching the rank
+                if (c >= rank) {                                  // first bucket reaching the rank
                     double fixed_prev = -INFINITY;
-                    if (b > 0) fixed_prev = fmax(div_const(CG_SA(L, k) * g.f[s], a.range_s, a.rc_range), CG_ST(L, kFB, tt));
-                    const double r = interpolate_quantile(a.le, b, cval[s], fixed_prev, rank);
+                    if (b > 0) {
+                        fixed_prev = CG_ST(L, kFB, tt);
+                        const double pw = pick_window(prevw, k);
+                        if (pw > -INFINITY) fixed_prev = fmax(div_const(pw * fs, a.range_s, a.rc_range), fixed_prev);
+                    }
+                    const double r = interpolate_quantile(a.le, b, c, fixed_prev, rank);
                     found |= bit;
                     CG_EMUL_STAT(captures, 1);
-                    if (q == p.gate_q) CG_ST(L, kFQC, tt) = r;
+                    if (q == p.gate_q) gate_quantile_known(a, L, ver, tt, delta, r, pass_bits);
                     if (a.metrics) a.metrics[((size_t)pv * p.n_ticks + tick_base + tt) * W + q] = r;
                 } else {
                     y = fmin(y, win_threshold(rank, g.rinv[s]));
                 }
             }
-            if (clamped) CG_ST(L, kFB, tt) = fmax(CG_ST(L, kFB, tt), cval[s]);
+            if ((clamped >> s) & 1u) CG_ST(L, kFB, tt) = fmax(CG_ST(L, kFB, tt), c);
         }
-        if (clamped) excl |= 1u << k;
+        if (clamped) {
+            // the window stays out of the running maximum for this row: ticks of the window that
+            // were not clamped themselves put their value into their per-tick maximum, too
+            excl |= 1u << k;
+            const unsigned rest = hosted & ~clamped;
+#pragma unroll 1
+            for (int s = 0; s < 3; ++s) {
+                if (!((rest >> s) & 1u)) continue;
+                const int tt = 3 * ((k - lg.dl - g.off[s]) >> 1) + s;
+                CG_ST(L, kFB, tt) = fmax(CG_ST(L, kFB, tt), div_const(res * g.f[s], a.range_s, a.rc_range));
+            }
+        }
         CG_EMUL_STAT(clamps, clamped ? 1 : 0);
         CG_SY(L, k) = y;
     }
@@ -500,29 +562,18 @@ CG_DEVINL unsigned bucket_events(const WarpArgs& a, const SlotGeom& g, LaneGeo& 
 
 // After the last bucket row: the speculation "the +Inf bucket holds the observations" is checked
 // per tick (Appendix A step 3-4: observations = the running maximum over ALL buckets).  The caller
-// has left the final window maxima in the scratch column.  Then the quantile part of the gate (:440).
-CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, int ver,
-                             int delta, unsigned& fb, unsigned& pass_bits) {
-    const cg_params& p = a.p;
+// has left the final window maxima in the scratch column.
+CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, unsigned& fb) {
 #pragma unroll 1
-    for (int tt = 0; tt < kLaneTicks; ++tt) {
-        if (!((lg.act >> tt) & 1u)) continue;
-        const int s = tt % 3, k = lane_window(g, lg, tt);
-        const double pvw = CG_SA(L, k);
-        double fixed = CG_ST(L, kFB, tt);
-        if (pvw > -INFINITY) fixed = fmax(div_const(pvw * g.f[s], a.range_s, a.rc_range), fixed);
-        if (!(fixed <= CG_ST(L, kFA, tt))) { fb |= 1u << tt; lg.act &= ~(1u << tt); continue; }
-        const double qv = CG_ST(L, kFQC, tt);
-        if (ver == 0) {
-            CG_ST(L, kFSQ, tt) = qv;
-        } else {
-            int tn = tt + delta, ln = L.lane;
-            if (tn < 0) { tn += kLaneTicks; --ln; }
-            if (tn >= kLaneTicks) { tn -= kLaneTicks; ++ln; }
-            if (ln >= 0 && ln < 32) {
-                const double q_n = (L.st + (ln - L.lane))[(kFSQ * kLaneTicks + tn) * 32];
-                if (q_n <= qv * p.one_plus_thr[0]) pass_bits |= 1u << tt;          // :440
-            }
+    for (int kk = 0; kk < kG; ++kk) {
+#pragma unroll 1
+        for (int s = 0; s < 3; ++s) {
+            const int tt = 3 * kk + s;
+            if (!((lg.act >> tt) & 1u)) continue;
+            const double pvw = CG_SY(L, 2 * kk + g.off[s] + lg.dl);
+            double fixed = CG_ST(L, kFB, tt);
+            if (pvw > -INFINITY) fixed = fmax(div_const(pvw * g.f[s], a.range_s, a.rc_range), fixed);
+            if (!(fixed <= CG_ST(L, kFA, tt))) { fb |= 1u << tt; lg.act &= ~(1u << tt); }
         }
     }
 }
@@ -531,8 +582,9 @@ CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, 
 // ymin = smallest delta that may reach a rank still searched
 template <typename T, int NQ, typename AnyFn>
 CG_DEVINL void bucket_row(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                          const T* __restrict__ tile, int b, int64_t pv, int tick_base, double (&prevw)[kLaneWin],
-                          double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb, AnyFn any) {
+                          const T* __restrict__ tile, int b, int ver, int delta, int64_t pv, int tick_base,
+                          double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
+                          unsigned& pass_bits, AnyFn any) {
     double x[kTile], w[kLaneWin];
     TileLoad<T>::load(tile, x);
     window_deltas(x, w);
@@ -542,28 +594,30 @@ CG_DEVINL void bucket_row(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, con
     CG_EMUL_STAT(reset, rflag ? 1 : 0);
     if (any(rflag)) {
         fix_resets(x, w);
-        const bool c0 = !(x[0] * gmin >= w[0]) | !(x[1] * gmin >= w[1]) | !(x[2] * gmin >= w[2]);
-        const bool c1 = !(x[3] * gmin >= w[3]) | !(x[4] * gmin >= w[4]) | !(x[5] * gmin >= w[5]);
-        const bool c2 = !(x[6] * gmin >= w[6]) | !(x[7] * gmin >= w[7]) | !(x[8] * gmin >= w[8]);
-        cflag = c0 | c1 | c2;
+        bool c[3] = {false, false, false};
+#pragma unroll
+        for (int k = 0; k < kLaneWin; ++k) c[k % 3] |= !(x[k] * gmin >= w[k]);
+        cflag = c[0] | c[1] | c[2];
     } else {
         // no reset in the tile: samples are non-decreasing, so every window delta is at most
-        // x[11]-x[0] and every first sample at least x[0]
+        // x[last]-x[0] and every first sample at least x[0]
         cflag = !(x[0] * gmin >= x[kTile - 1] - x[0]);
     }
-    const bool h0 = !(w[0] < ymin[0]) | !(w[1] < ymin[1]) | !(w[2] < ymin[2]);
-    const bool h1 = !(w[3] < ymin[3]) | !(w[4] < ymin[4]) | !(w[5] < ymin[5]);
-    const bool h2 = !(w[6] < ymin[6]) | !(w[7] < ymin[7]) | !(w[8] < ymin[8]);
-    const bool ev = (cflag | h0 | h1 | h2) && lg.host != 0u;
+    bool h[3] = {false, false, false};
+#pragma unroll
+    for (int k = 0; k < kLaneWin; ++k) h[k % 3] |= !(w[k] < ymin[k]);
+    const bool hflag = h[0] | h[1] | h[2];
+    const bool ev = (cflag | hflag) && lg.host != 0u;
     CG_EMUL_STAT(event, ev ? 1 : 0);
+    CG_EMUL_STAT(cfl, (cflag && lg.host != 0u) ? 1 : 0);
+    CG_EMUL_STAT(hfl, (hflag && lg.host != 0u) ? 1 : 0);
     if (any(ev)) {
         unsigned mask = 0u;
 #pragma unroll
-        for (int k = 0; k < kLaneWin; ++k) {
+        for (int k = 0; k < kLaneWin; ++k)
             if (!(x[k] * gmin >= w[k]) || !(w[k] < ymin[k])) mask |= 1u << k;
-            CG_SA(L, k) = prevw[k];
-        }
-        const unsigned excl = bucket_events<T, NQ>(a, g, lg, L, tile, b, mask & lg.host, pv, tick_base, found, fb);
+        const unsigned excl = bucket_events<T, NQ>(a, g, lg, L, tile, b, mask & lg.host, prevw, ver, delta, pv, tick_base,
+                                                   found, fb, pass_bits);
 #pragma unroll
         for (int k = 0; k < kLaneWin; ++k) {
             if ((excl >> k) & 1u) w[k] = -INFINITY;
@@ -738,39 +792,49 @@ struct WarpAny {
 struct FillCursor {
     int64_t pair;
     int chunk, u;
+    const char* sc;     // first scalar / bucket row of the pair
+    const char* bk;
 };
 
+// CTA-wide barrier that a single-warp CTA does not need
+__device__ __forceinline__ void pair_sync() {
+    if (kWarps > 1) __syncthreads();
+    else __syncwarp();
+}
+
 template <typename T, int NQ>
-__global__ void __launch_bounds__(32, 7)
+__global__ void __launch_bounds__(kLanes, kG == 4 ? 7 : kG == 2 ? 8 : 4)
 warp_kernel(const __grid_constant__ WarpArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const cg_params& p = a.p;
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + a.off_bars);
-    SlotGeom* geo = reinterpret_cast<SlotGeom*>(smem + a.off_geom);
+    SlotGeom* geo = reinterpret_cast<SlotGeom*>(smem + a.off_geom) + 2 * warp;   // each warp keeps its own copy
     const int n_words = (p.n_ticks + 31) >> 5;
     uint32_t* s_bits = reinterpret_cast<uint32_t*>(smem + a.off_bits);   // promote bits of the pair
     uint32_t* s_fb = s_bits + n_words;                                   // ticks for the exact fallback
     const FillEntry* s_tab = reinterpret_cast<const FillEntry*>(smem + a.off_tab);
     Lane L;
-    L.lane = lane;
-    L.st = reinterpret_cast<double*>(smem + a.off_state) + lane;
-    L.sa = reinterpret_cast<double*>(smem + a.off_scratch) + lane;
+    L.lane = tid;
+    L.st = reinterpret_cast<double*>(smem + a.off_state) + tid;
+    L.sa = reinterpret_cast<double*>(smem + a.off_scratch) + tid;
     const int B = p.n_buckets, W = p.n_q + CG_M_EXTRA, pitch = p.row_pitch;
     const int n_sc = a.n_sc_uses, n_bk = a.n_bk_uses, n_slots = a.n_slots;
     const WarpAny any;
-    if (lane == 0) {
+    if (tid == 0) {
         for (int s = 0; s < n_slots; ++s) mbar_init(bars + s, 1);
         mbar_init_fence();
     }
-    for (int u = lane; u < a.uses_per_pass; u += 32) reinterpret_cast<FillEntry*>(smem + a.off_tab)[u] = fill_entry(a, u);
-    __syncwarp();
+    for (int u = tid; u < a.uses_per_pass; u += kLanes) reinterpret_cast<FillEntry*>(smem + a.off_tab)[u] = fill_entry(a, u);
+    pair_sync();
     const QuantConst qc = quant_const(a);
 
-    // ---- the ring: this warp is producer and consumer --------------------------------------
+    // ---- the ring: the pair's warps are its consumers, thread 0 its producer -----------------
     const size_t pair_bytes_sc = (size_t)2 * p.n_scalar * a.row_bytes, pair_bytes_bk = (size_t)2 * B * a.row_bytes;
     auto skip_pairs = [&](FillCursor& c) {
         while (c.pair < a.n_pairs && a.has_previous && !a.has_previous[c.pair]) c.pair += gridDim.x;
+        c.sc = reinterpret_cast<const char*>(a.scalars) + c.pair * pair_bytes_sc;
+        c.bk = reinterpret_cast<const char*>(a.buckets) + c.pair * pair_bytes_bk;
     };
     auto cursor_next = [&](FillCursor& c) {
         if (++c.u == a.uses_per_pass) {
@@ -778,11 +842,9 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
             if (++c.chunk == a.n_chunks) { c.chunk = 0; c.pair += gridDim.x; skip_pairs(c); }
         }
     };
-    auto issue_fill = [&](const FillCursor& c, uint32_t slot) {      // one lane
+    auto issue_fill = [&](const FillCursor& c, uint32_t slot) {      // one thread
         const FillEntry e = s_tab[c.u];
-        const bool bk = (e.meta >> 31) != 0;
-        const char* src = (bk ? reinterpret_cast<const char*>(a.buckets) + c.pair * pair_bytes_bk
-                              : reinterpret_cast<const char*>(a.scalars) + c.pair * pair_bytes_sc) + e.off;
+        const char* src = ((e.meta >> 31) ? c.bk : c.sc) + e.off;
         const uint32_t bytes = e.meta & 0x7fffffffu;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // reads of the slot before the async write
         mbar_arrive_expect_tx(bars + slot, bytes);
@@ -792,7 +854,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
     fill.pair = blockIdx.x; fill.chunk = 0; fill.u = 0;
     skip_pairs(fill);
     for (int s = 0; s < n_slots; ++s) {          // prologue: fill the whole ring
-        if (lane == 0 && fill.pair < a.n_pairs) issue_fill(fill, (uint32_t)s);
+        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, (uint32_t)s);
         cursor_next(fill);
     }
     uint32_t head = 0, head_parity = 0;           // oldest slot in use and the parity of its mbarrier
@@ -802,8 +864,8 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         mbar_wait(bars + s, par);
         return reinterpret_cast<const T*>(smem + (size_t)s * a.slot_bytes);
     };
-    auto slot_release = [&]() {                   // the head slot; callers have synchronised the warp
-        if (lane == 0 && fill.pair < a.n_pairs) issue_fill(fill, head);
+    auto slot_release = [&]() {                   // the head slot; callers have synchronised the pair's warps
+        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, head);
         cursor_next(fill);
         if (++head == (uint32_t)n_slots) { head = 0; head_parity ^= 1u; }
     };
@@ -812,11 +874,11 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         const bool hp = a.has_previous ? a.has_previous[pair] != 0 : true;
         if (!hp) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
-            if (lane == 0 && a.decisions) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
-            if (a.gate_bits) for (int w = lane; w < n_words; w += 32) a.gate_bits[pair * n_words + w] = 0u;
+            if (tid == 0 && a.decisions) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
+            if (a.gate_bits) for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = 0u;
             continue;
         }
-        for (int w = lane; w < 2 * n_words; w += 32) s_bits[w] = 0u;
+        for (int w = tid; w < 2 * n_words; w += kLanes) s_bits[w] = 0u;
         const int32_t phase0 = a.phase[pair * 2], phase1 = a.phase[pair * 2 + 1];
 #pragma unroll 1
         for (int chunk = 0; chunk < a.n_chunks; ++chunk) {
@@ -832,7 +894,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
 #pragma unroll
             for (int ver = 0; ver < 2; ++ver) {
                 unsigned vt;
-                lg[ver] = lane_setup(a, geo[ver], lane, chunk0, chunk_end, vt);
+                lg[ver] = lane_setup(a, geo[ver], tid, chunk0, chunk_end, vt);
                 fbm[ver] = vt & ~lg[ver].act;
             }
 
@@ -846,9 +908,9 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     if (s >= (uint32_t)n_slots) s -= n_slots;
                     return reinterpret_cast<const T*>(smem + (size_t)s * a.slot_bytes) + (r % kRowsPerUse) * pitch;
                 };
-                scalar_phase<T>(a, geo[ver], lg[ver], L, ver, pair * 2 + ver, geo[ver].j0 + kLaneTicks * lane, delta,
+                scalar_phase<T>(a, geo[ver], lg[ver], L, ver, pair * 2 + ver, geo[ver].j0 + kLaneTicks * tid, delta,
                                 row_ptr, pass_sc);
-                __syncwarp();
+                pair_sync();
                 for (int i = 0; i < n_sc; ++i) slot_release();
             }
 
@@ -858,17 +920,17 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 for (int ver = 0; ver < 2; ++ver) {
                     const SlotGeom& g = geo[ver];
                     const int64_t pv = pair * 2 + ver;
-                    const int tick_base = g.j0 + kLaneTicks * lane;
+                    const int tick_base = g.j0 + kLaneTicks * tid;
                     LaneGeo l = lg[ver];
                     unsigned fb = fbm[ver];
                     double prevw[kLaneWin], ymin[kLaneWin];
                     uint64_t found = ~0ull;
                     {
                         const T* rows = slot_wait(0);
-                        inf_row_setup<T, NQ>(a, g, l, L, qc, rows + l.bt, pv, tick_base, found, fb);
+                        inf_row_setup<T, NQ>(a, g, l, L, qc, rows + l.bt, ver, delta, pv, tick_base, found, fb, pass_q);
 #pragma unroll
                         for (int k = 0; k < kLaneWin; ++k) { ymin[k] = CG_SY(L, k); prevw[k] = -INFINITY; }
-                        __syncwarp();
+                        pair_sync();
                         slot_release();
                     }
 #pragma unroll 1
@@ -877,44 +939,47 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                         const int first = u * kRowsPerUse, nr = min(kRowsPerUse, B - 1 - first);
 #pragma unroll 1
                         for (int r = 0; r < nr; ++r)
-                            bucket_row<T, NQ>(a, g, l, L, rows + r * pitch + l.bt, first + r, pv, tick_base, prevw, ymin,
-                                              found, fb, any);
-                        __syncwarp();
+                            bucket_row<T, NQ>(a, g, l, L, rows + r * pitch + l.bt, first + r, ver, delta, pv, tick_base,
+                                              prevw, ymin, found, fb, pass_q, any);
+                        pair_sync();
                         slot_release();
                     }
 #pragma unroll
-                    for (int k = 0; k < kLaneWin; ++k) CG_SA(L, k) = prevw[k];
-                    bucket_finish(a, g, l, L, ver, delta, fb, pass_q);
+                    for (int k = 0; k < kLaneWin; ++k) CG_SY(L, k) = prevw[k];
+                    bucket_finish(a, g, l, L, fb);
                     fbm[ver] = fb;
                     if (ver == 1) act_old = l.act;
-                    __syncwarp();
+                    pair_sync();
                 }
             } else {
                 act_old = lg[1].act;
             }
-            if (!(p.checks & CG_G_P95_OK)) pass_q = 0xfffu;
+            if (!(p.checks & CG_G_P95_OK)) pass_q = (1u << kLaneTicks) - 1u;
 
             // ---- this pass's bits: promote bits from the old version's lanes, fallback ticks from both
             {
-                const BitField pb = place_bits(pass_sc & pass_q & act_old, geo[1].j0 + kLaneTicks * lane);
+                const BitField pb = place_bits(pass_sc & pass_q & act_old, geo[1].j0 + kLaneTicks * tid);
                 if (pb.lo) atomicOr(s_bits + pb.word0, pb.lo);
                 if (pb.hi) atomicOr(s_bits + pb.word0 + 1, pb.hi);
 #pragma unroll
                 for (int ver = 0; ver < 2; ++ver) {
-                    const BitField f = place_bits(fbm[ver], geo[ver].j0 + kLaneTicks * lane);
+                    const BitField f = place_bits(fbm[ver], geo[ver].j0 + kLaneTicks * tid);
                     if (f.lo) atomicOr(s_fb + f.word0, f.lo);
                     if (f.hi) atomicOr(s_fb + f.word0 + 1, f.hi);
                 }
             }
         }
-        __syncwarp();
-        // ---- exact re-evaluation of whatever the fast path could not decide
+        pair_sync();
+        // ---- exact re-evaluation of whatever the fast path could not decide (the pair's warps take
+        // the fallback ticks in turn)
+        int fb_seq = 0;
 #pragma unroll 1
         for (int wd = 0; wd < n_words; ++wd) {
             uint32_t todo = s_fb[wd];
             while (todo) {
                 const int bit = __ffs(todo) - 1;
                 todo &= todo - 1;
+                if ((fb_seq++ % kWarps) != warp) continue;
                 const int tick = wd * 32 + bit;
                 double mn[CG_MAX_Q + CG_M_EXTRA], mo[CG_MAX_Q + CG_M_EXTRA];
                 uint8_t vn, vo;
@@ -923,9 +988,8 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 if (lane == 0) {
                     const double nm[3] = {p.n_q > 0 ? mn[p.gate_q] : NAN, mn[p.n_q + CG_M_ERROR_RATE], mn[p.n_q + CG_M_LATENCY_AVG]};
                     const double om[3] = {p.n_q > 0 ? mo[p.gate_q] : NAN, mo[p.n_q + CG_M_ERROR_RATE], mo[p.n_q + CG_M_LATENCY_AVG]};
-                    uint32_t wv = s_bits[wd] & ~(1u << bit);
-                    if (gate_eval(nm, vn, om, vo, p) & CG_G_PROMOTE) wv |= 1u << bit;
-                    s_bits[wd] = wv;
+                    if (gate_eval(nm, vn, om, vo, p) & CG_G_PROMOTE) atomicOr(s_bits + wd, 1u << bit);
+                    else atomicAnd(s_bits + wd, ~(1u << bit));
                     if (a.metrics) {
                         double* on = a.metrics + ((size_t)(pair * 2) * p.n_ticks + tick) * W;
                         double* oo = a.metrics + ((size_t)(pair * 2 + 1) * p.n_ticks + tick) * W;
@@ -938,14 +1002,14 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 }
             }
         }
-        __syncwarp();
+        pair_sync();
         // ---- the step loop (:296-361) over the pair's promote bits
-        if (a.gate_bits) for (int w = lane; w < n_words; w += 32) a.gate_bits[pair * n_words + w] = s_bits[w];
-        if (lane == 0 && a.decisions) {
+        if (a.gate_bits) for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = s_bits[w];
+        if (tid == 0 && a.decisions) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
             a.decisions[pair] = replay_schedule_bits(s_bits, n_words, true, st_tick, p);
         }
-        __syncwarp();
+        pair_sync();
     }
 }
 
@@ -955,7 +1019,7 @@ cudaError_t launch_warp_tn(const WarpArgs& a, int grid, cudaStream_t s) {
     auto kern = warp_kernel<T, NQ>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a.smem_bytes);
     if (e != cudaSuccess) return e;
-    kern<<<grid, 32, a.smem_bytes, s>>>(a);
+    kern<<<grid, kLanes, a.smem_bytes, s>>>(a);
     return cudaGetLastError();
 }
 #endif  // __CUDACC__

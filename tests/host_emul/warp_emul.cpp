@@ -1,7 +1,7 @@
 // warp_emul.cpp -- HOST emulation of the streaming kernel's per-lane arithmetic (csrc/cg_warp.cuh).
 //
 // TEST INFRASTRUCTURE ONLY.  The lane functions of cg_warp.cuh are plain C++ as well; this file
-// drives them with the same sequence of phases the CUDA kernel uses (32 lanes emulated one after
+// drives them with the same sequence of phases the CUDA kernel uses (the pair's lanes emulated one after
 // the other, warp votes replaced by "my own flag", or by "always" to prove that every rare path is
 // neutral), so that the arithmetic can be compared with the oracle on a machine without a GPU.
 // Ticks the fast path hands to the exact fallback are evaluated here by a plain sequential
@@ -102,14 +102,14 @@ void exact_tick(const WarpArgs& a, int64_t pv, int32_t phase, int tick, double* 
     valid_out = valid;
 }
 
-struct Counters { long long fb_ticks, event_rows, rows, reset_rows, event_iters, captures, clamps, windows; };
+struct Counters { long long fb_ticks, event_rows, rows, reset_rows, event_iters, captures, clamps, windows, cfl_rows, hfl_rows; };
 
 template <typename T, int NQ>
 void emulate(const WarpArgs& a, bool force_rare, Counters* cnt) {
     const cg_params& p = a.p;
     const int K = p.n_scalar, B = p.n_buckets, W = p.n_q + CG_M_EXTRA, pitch = p.row_pitch;
     const int n_words = (p.n_ticks + 31) >> 5;
-    std::vector<double> st((size_t)kFields * kLaneTicks * 32), sa((size_t)2 * kLaneWin * 32);
+    std::vector<double> st((size_t)kFields * kLaneTicks * kLanes), sa((size_t)kLaneWin * kLanes);
     std::vector<uint32_t> s_bits(n_words), s_fb(n_words);
     const QuantConst qc = quant_const(a);
     const HostAny any{force_rare};
@@ -129,10 +129,10 @@ void emulate(const WarpArgs& a, bool force_rare, Counters* cnt) {
             const int chunk0 = chunk * kChunkTicks, chunk_end = std::min(p.n_ticks, chunk0 + kChunkTicks);
             host_geometry(a, phase0, chunk0, geo);
             host_geometry(a, phase1, chunk0, geo + 1);
-            LaneGeo lg[2][32];
-            unsigned fbm[2][32], pass_sc[32], pass_q[32];
-            Lane L[32];
-            for (int lane = 0; lane < 32; ++lane) {
+            LaneGeo lg[2][kLanes];
+            unsigned fbm[2][kLanes], pass_sc[kLanes], pass_q[kLanes];
+            Lane L[kLanes];
+            for (int lane = 0; lane < kLanes; ++lane) {
                 L[lane].lane = lane; L[lane].st = st.data() + lane; L[lane].sa = sa.data() + lane;
                 pass_sc[lane] = pass_q[lane] = 0u;
                 for (int ver = 0; ver < 2; ++ver) {
@@ -147,7 +147,7 @@ void emulate(const WarpArgs& a, bool force_rare, Counters* cnt) {
                 const int64_t pv = pair * 2 + ver;
                 const T* sc = reinterpret_cast<const T*>(a.scalars) + (size_t)pv * K * pitch;
                 auto row_ptr = [&](int r) -> const T* { return sc + (size_t)r * pitch; };
-                for (int lane = 0; lane < 32; ++lane)
+                for (int lane = 0; lane < kLanes; ++lane)
                     scalar_phase<T>(a, g, lg[ver][lane], L[lane], ver, pv, g.j0 + kLaneTicks * lane, delta, row_ptr, pass_sc[lane]);
             }
             if (B > 0) {
@@ -156,38 +156,40 @@ void emulate(const WarpArgs& a, bool force_rare, Counters* cnt) {
                     const int64_t pv = pair * 2 + ver;
                     const T* bk = reinterpret_cast<const T*>(a.buckets) + (size_t)pv * B * pitch;
                     // row-outer, lane-inner, like the warp: lets the statistics see warp-level votes
-                    double prevw[32][kLaneWin], ymin[32][kLaneWin];
-                    uint64_t found[32];
-                    for (int lane = 0; lane < 32; ++lane) {
+                    double prevw[kLanes][kLaneWin], ymin[kLanes][kLaneWin];
+                    uint64_t found[kLanes];
+                    for (int lane = 0; lane < kLanes; ++lane) {
                         LaneGeo& l = lg[ver][lane];
                         const T* tile = bk + (size_t)(B - 1) * pitch + l.bt;
                         found[lane] = ~0ull;
-                        inf_row_setup<T, NQ>(a, g, l, L[lane], qc, tile, pv, g.j0 + kLaneTicks * lane, found[lane], fbm[ver][lane]);
+                        inf_row_setup<T, NQ>(a, g, l, L[lane], qc, tile, ver, delta, pv, g.j0 + kLaneTicks * lane, found[lane],
+                                             fbm[ver][lane], pass_q[lane]);
                         for (int k = 0; k < kLaneWin; ++k) { ymin[lane][k] = CG_SY(L[lane], k); prevw[lane][k] = -INFINITY; }
                     }
                     for (int b = 0; b < B - 1; ++b) {
-                        int w_reset = 0, w_event = 0, w_iter = 0;
-                        for (int lane = 0; lane < 32; ++lane) {
+                        int w_reset = 0, w_event = 0, w_iter = 0, w_cfl = 0, w_hfl = 0;
+                        for (int lane = 0; lane < kLanes; ++lane) {
                             LaneGeo& l = lg[ver][lane];
                             // the event loop works from the scratch columns: thresholds live there per lane
                             for (int k = 0; k < kLaneWin; ++k) CG_SY(L[lane], k) = ymin[lane][k];
-                            g_emul_row = EmulRowStat{0, 0, 0, 0, 0};
-                            bucket_row<T, NQ>(a, g, l, L[lane], bk + (size_t)b * pitch + l.bt, b, pv, g.j0 + kLaneTicks * lane,
-                                              prevw[lane], ymin[lane], found[lane], fbm[ver][lane], any);
-                            w_reset |= g_emul_row.reset; w_event |= g_emul_row.event;
+                            g_emul_row = EmulRowStat{0, 0, 0, 0, 0, 0, 0};
+                            bucket_row<T, NQ>(a, g, l, L[lane], bk + (size_t)b * pitch + l.bt, b, ver, delta, pv,
+                                              g.j0 + kLaneTicks * lane, prevw[lane], ymin[lane], found[lane], fbm[ver][lane],
+                                              pass_q[lane], any);
+                            w_reset |= g_emul_row.reset; w_event |= g_emul_row.event; w_cfl |= g_emul_row.cfl; w_hfl |= g_emul_row.hfl;
                             w_iter = std::max(w_iter, g_emul_row.windows);
                             if (cnt) { cnt->captures += g_emul_row.captures; cnt->clamps += g_emul_row.clamps; cnt->windows += g_emul_row.windows; }
                         }
-                        if (cnt) { ++cnt->rows; cnt->reset_rows += w_reset; cnt->event_rows += w_event; cnt->event_iters += w_iter; }
+                        if (cnt) { ++cnt->rows; cnt->reset_rows += w_reset; cnt->event_rows += w_event; cnt->event_iters += w_iter; cnt->cfl_rows += w_cfl; cnt->hfl_rows += w_hfl; }
                     }
-                    for (int lane = 0; lane < 32; ++lane) {
-                        for (int k = 0; k < kLaneWin; ++k) CG_SA(L[lane], k) = prevw[lane][k];
-                        bucket_finish(a, g, lg[ver][lane], L[lane], ver, delta, fbm[ver][lane], pass_q[lane]);
+                    for (int lane = 0; lane < kLanes; ++lane) {
+                        for (int k = 0; k < kLaneWin; ++k) CG_SY(L[lane], k) = prevw[lane][k];
+                        bucket_finish(a, g, lg[ver][lane], L[lane], fbm[ver][lane]);
                     }
                 }
             }
-            for (int lane = 0; lane < 32; ++lane) {
-                if (!(p.checks & CG_G_P95_OK)) pass_q[lane] = 0xfffu;
+            for (int lane = 0; lane < kLanes; ++lane) {
+                if (!(p.checks & CG_G_P95_OK)) pass_q[lane] = (1u << kLaneTicks) - 1u;
                 const BitField pb = place_bits(pass_sc[lane] & pass_q[lane] & lg[1][lane].act, geo[1].j0 + kLaneTicks * lane);
                 if (pb.lo) s_bits[pb.word0] |= pb.lo;
                 if (pb.hi) s_bits[pb.word0 + 1] |= pb.hi;
@@ -236,9 +238,10 @@ void emulate(const WarpArgs& a, bool force_rare, Counters* cnt) {
 }  // namespace
 
 // Same arguments as cg_eval_fused, HOST pointers.  force_rare != 0: every warp vote answers "yes".
-// counters (may be NULL, 8 entries): [0] ticks handed to the exact fallback, [1] warp-rows that entered the event
+// counters (may be NULL, 10 entries): [0] ticks handed to the exact fallback, [1] warp-rows that entered the event
 // loop, [2] bucket warp-rows, [3] warp-rows with a reset correction, [4] event-loop iterations (max over lanes, summed
-// over rows), [5] quantile captures, [6] clamped windows, [7] windows looked at.
+// over rows), [5] quantile captures, [6] clamped windows, [7] windows looked at,
+// [8] warp-rows where the clamp pre-test fired, [9] warp-rows where a rank threshold fired.
 extern "C" int emul_eval_fused(const void* scalars, const void* buckets, const double* le, const int32_t* phase,
                                const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
                                const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
@@ -254,7 +257,7 @@ extern "C" int emul_eval_fused(const void* scalars, const void* buckets, const d
     a.n_pairs = n_pairs;
     a.p = *p;
     cg::fill_warp_constants(a);
-    Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
+    Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     const bool f = force_rare != 0;
     const int nq = p->n_q < 1 ? 1 : p->n_q;
     if (p->dtype == CG_F32) {
@@ -273,6 +276,7 @@ extern "C" int emul_eval_fused(const void* scalars, const void* buckets, const d
         }
     }
     if (counters) { counters[0] = c.fb_ticks; counters[1] = c.event_rows; counters[2] = c.rows; counters[3] = c.reset_rows;
-                    counters[4] = c.event_iters; counters[5] = c.captures; counters[6] = c.clamps; counters[7] = c.windows; }
+                    counters[4] = c.event_iters; counters[5] = c.captures; counters[6] = c.clamps; counters[7] = c.windows;
+                    counters[8] = c.cfl_rows; counters[9] = c.hfl_rows; }
     return CG_OK;
 }

@@ -44,7 +44,7 @@ def emulate(b, p, force_rare=False, has_previous=None, start_tick=None):
     bits = np.zeros((n, p.n_words), np.uint32)
     m = np.full((n, 2, p.n_ticks, p.metric_width), -12345.0)
     v = np.full((n, 2, p.n_ticks), 255, np.uint8)
-    cnt = np.zeros(8, np.int64)
+    cnt = np.zeros(10, np.int64)
     ptr = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)  # noqa: E731
     rc = lib.emul_eval_fused(ptr(b.scalars), ptr(b.buckets) if p.n_buckets else None, ptr(b.le) if p.n_buckets else None,
                              ptr(b.phase), ptr(has_previous), ptr(start_tick), n, C.byref(p), ptr(dec), ptr(bits),
