@@ -12,7 +12,7 @@ _vp, _i64 = C.c_void_p, C.c_int64
 
 
 def _load():
-    path = _build.LIB
+    path = os.environ.get("CG_LIB_PATH") or _build.LIB    # CG_LIB_PATH: developer aid, a differently tuned build
     if not os.path.exists(path):
         try:
             _build.build()

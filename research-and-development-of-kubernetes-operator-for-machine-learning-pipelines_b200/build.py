@@ -28,6 +28,10 @@ CFLAGS = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-fmad=false", "-Xcompiler", 
 def _units():
     # CG_ABLATE=1: developer build with the tuning knobs (ring depth, CTAs per SM) read from the environment
     extra = ["-DCG_ABLATE"] if os.environ.get("CG_ABLATE") else []
+    if os.environ.get("CG_MIN_CTAS"):                # developer build: register budget of the streaming kernel
+        extra += [f"-DCG_MIN_CTAS={int(os.environ['CG_MIN_CTAS'])}"]
+    if os.environ.get("CG_ROWS_PER_USE"):            # developer build: rows per ring slot
+        extra += [f"-DCG_ROWS_PER_USE={int(os.environ['CG_ROWS_PER_USE'])}"]
     if os.environ.get("CG_G"):                       # developer build: periods of the tick grid per lane (1, 2 or 4)
         extra += [f"-DCG_G={int(os.environ['CG_G'])}"]
     units = [("cg_api", "cg_api.cu", extra)]

@@ -58,7 +58,10 @@ constexpr int kLaneTicks = 3 * kG;         // ticks per lane
 constexpr int kLaneWin = 2 * kG + 1;       // window start positions per lane tile
 constexpr int kTile = 2 * kG + 4;          // samples per lane tile
 constexpr int kChunkTicks = 382;           // ticks one pass over the rows covers (384 minus the rotation slack)
-constexpr int kRowsPerUse = 2;     // rows per ring slot
+#ifndef CG_ROWS_PER_USE
+#define CG_ROWS_PER_USE 2
+#endif
+constexpr int kRowsPerUse = CG_ROWS_PER_USE;   // rows per ring slot
 constexpr unsigned kFullMask = 0xffffffffu;
 
 #ifndef __CUDACC__
@@ -802,8 +805,11 @@ __device__ __forceinline__ void pair_sync() {
     else __syncwarp();
 }
 
+#ifndef CG_MIN_CTAS
+#define CG_MIN_CTAS (kG == 4 ? 7 : kG == 2 ? 8 : 4)
+#endif
 template <typename T, int NQ>
-__global__ void __launch_bounds__(kLanes, kG == 4 ? 7 : kG == 2 ? 8 : 4)
+__global__ void __launch_bounds__(kLanes, CG_MIN_CTAS)
 warp_kernel(const __grid_constant__ WarpArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const cg_params& p = a.p;

@@ -25,8 +25,7 @@ else:
     b = synth.generate(p, n, seed=1234, adversarial=0.01)
 dec, bits, m, v, c = T.emulate(b, p)
 rows = max(int(c[2]), 1)
-print(f"{src}: pairs {n} warp-rows {rows}  reset_rows {c[3] / rows:.3f}  event_rows {c[1] / rows:.3f}  clamp-pretest rows {c[8] / rows:.3f}  "
-      f"threshold rows {c[9] / rows:.3f}  iters/row {c[4] / rows:.3f}  windows/row {c[7] / rows:.2f}  clamped windows/row {c[6] / rows:.3f}  "
+print(f"{src}: pairs {n} warp-rows {rows}  reset_rows {c[3] / rows:.3f}  event_rows {c[1] / rows:.3f}  iters/row {c[4] / rows:.3f}  windows/row {c[7] / rows:.2f}  clamped windows/row {c[6] / rows:.3f}  "
       f"captures/pair {c[5] / n:.0f}  fallback ticks/pair {c[0] / n:.2f}")
 d = np.diff(b.buckets[:, :, :, :p.n_samples], axis=-1)
 print("resets per bucket row:", float((d < 0).sum()) / (n * 2 * p.n_buckets), " first sample median", float(np.median(b.buckets[..., 0])),
