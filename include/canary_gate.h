@@ -8,8 +8,9 @@
  * documented as HOST memory, every data pointer is DEVICE memory owned by the
  * caller.  All work is enqueued on the `stream` argument (a cudaStream_t passed as
  * void*, NULL = the legacy default stream) of the CURRENT device; nothing here
- * synchronises unless documented.  The library keeps no mutable global state and
- * allocates no device memory; callers pass workspaces.
+ * synchronises unless documented.  The library keeps no mutable global state (a launch
+ * counter for reporting aside), reads no environment variable and allocates no device
+ * memory: every kernel works in its inputs, its outputs and shared memory.
  *
  * Reference citations are file:line in /root/reference/mlflow_operator.py.
  *
@@ -120,7 +121,7 @@ typedef struct cg_params {
     int32_t max_attempts;        /* 10  (:293) */
     int32_t attempt_delay_ticks; /* attempt_delay / tick_step = 1 (:294) */
     int32_t start_tick;          /* tick at which the canary loop starts (:296) */
-    int32_t reserved;
+    int32_t reserved;            /* must be 0 (every entry point rejects anything else) */
     int32_t on_abort;            /* CG_ABORT_FREEZE (reference, default) | CG_ABORT_ROLLBACK */
 } cg_params;
 
@@ -219,7 +220,8 @@ int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase
 /* Same as cg_eval_fused with an explicit kernel choice: path 0 = automatic, 1 = the general
  * resident-tile kernel, 2 = the streaming kernel (CG_EINVAL if the geometry is not covered:
  * it needs window = 4 scrape periods and tick step = 2/3 period, the reference's constants
- * (:363, :294) with 15 s scrapes).  Both kernels give bit-identical results. */
+ * (:363, :294) with 15 s scrapes, at least 8 samples per series, at most 64 buckets and at
+ * least one scalar series).  Both kernels give bit-identical results. */
 int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const double* le,
                        const int32_t* phase, const uint8_t* has_previous, const int32_t* start_tick,
                        int64_t n_pairs, const cg_params* p, cg_decision* decisions,

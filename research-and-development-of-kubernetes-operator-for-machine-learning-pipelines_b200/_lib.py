@@ -38,8 +38,6 @@ def _load():
     lib.cg_stream_eligible.argtypes = [_vp]
     lib.cg_eval_irregular.argtypes = [_vp] * 9 + [_i64] + [_vp] * 6
     lib.cg_launch_info.argtypes = [_vp, _i64, _vp, _vp, _vp]
-    for name in OPTIONAL:
-        pass
     if lib.cg_abi_version() != 1:
         raise ImportError("libcanarygate.so ABI version mismatch; rebuild")
     probe = CgParams()
@@ -49,7 +47,6 @@ def _load():
     return lib
 
 
-OPTIONAL = ()
 LIB_PATH = _build.LIB
 lib = _load()
 

@@ -58,6 +58,7 @@ int check_params(const cg_params* p) {
     if (p->max_attempts < 1 || p->step < 1 || p->max_traffic < 1 || p->interval_ticks < 0 ||
         p->attempt_delay_ticks < 0 || p->init_current < 0)
         return fail(CG_EINVAL, "bad schedule constants");
+    if (p->reserved != 0) return fail(CG_EINVAL, "cg_params.reserved must be 0 (got %d): zero the struct or start from cg_params_default", p->reserved);
     if (p->on_abort != CG_ABORT_FREEZE && p->on_abort != CG_ABORT_ROLLBACK) return fail(CG_EINVAL, "on_abort must be CG_ABORT_FREEZE or CG_ABORT_ROLLBACK");
     if (p->attempt_delay_ticks == 0 && p->interval_ticks == 0)
         return fail(CG_EINVAL, "schedule never advances (both delays are 0 ticks)");

@@ -46,6 +46,7 @@ def test_params_struct_matches_header_defaults():
     (lambda p: setattr(p, "gate_q", 1), "gate_q"),
     (lambda p: setattr(p, "checks", 8), "checks"),
     (lambda p: setattr(p, "max_attempts", 0), "schedule"),
+    (lambda p: setattr(p, "reserved", 1), "reserved must be 0"),
 ])
 def test_bad_params_are_rejected_with_a_message(mut, frag):
     p = P.make_params()
@@ -64,3 +65,22 @@ def test_launch_info_reports_geometry_without_gpu():
     g, b, s = C.c_int32(), C.c_int32(), C.c_int32()
     assert _lib.lib.cg_launch_info(C.byref(p), 100000, C.byref(g), C.byref(b), C.byref(s)) == 0
     assert b.value % 32 == 0 and 0 < s.value <= 232448 and g.value >= 1
+
+
+def test_library_reads_no_environment_and_has_no_debug_switches():
+    """The shipped build has no tuning knobs: the ones the profiling tools use exist only in a
+    CG_ABLATE developer build (build.py), and cg_params.reserved is rejected unless 0."""
+    csrc = os.path.join(ROOT, "research-and-development-of-kubernetes-operator-for-machine-learning-pipelines_b200", "csrc")
+    for name in os.listdir(csrc):
+        text = open(os.path.join(csrc, name)).read()
+        out, depth = [], 0
+        for line in text.split("\n"):                       # drop #ifdef CG_ABLATE ... #endif blocks
+            if line.strip().startswith("#ifdef CG_ABLATE"):
+                depth += 1
+            elif depth and line.strip().startswith("#endif"):
+                depth -= 1
+            elif not depth:
+                out.append(line)
+        body = "\n".join(out)
+        assert "getenv" not in body, f"{name} reads the environment outside CG_ABLATE"
+        assert "p.reserved" not in body and "p->reserved &" not in body, f"{name} branches on cg_params.reserved"
