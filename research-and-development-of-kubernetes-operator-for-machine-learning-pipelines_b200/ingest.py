@@ -41,7 +41,10 @@ class IrregularSeries(ValueError):
 
 def parse_matrix(answer) -> List[Tuple[Dict[str, str], np.ndarray, np.ndarray]]:
     """One query_range answer (dict or JSON text) -> [(labels, ts_ms int64[], values fp64[])].
-    Prometheus sends sample values as strings ("NaN", "+Inf" included) and times as float seconds."""
+    Prometheus sends sample values as strings ("NaN", "+Inf" included) and times as float seconds;
+    both columns are converted with one vectorised numpy pass per series.  A list of
+    (labels, ts_ms, values) tuples -- `raw_series` output, what a remote-read client holds --
+    passes through untouched."""
     if isinstance(answer, (str, bytes)):
         answer = json.loads(answer)
     if isinstance(answer, dict) and "data" in answer:
@@ -54,11 +57,26 @@ def parse_matrix(answer) -> List[Tuple[Dict[str, str], np.ndarray, np.ndarray]]:
         answer = answer["result"]
     out = []
     for item in answer:
+        if isinstance(item, tuple):
+            labels, ts, v = item
+            out.append((dict(labels), np.asarray(ts, dtype=np.int64), np.asarray(v, dtype=np.float64)))
+            continue
         vals = item["values"]
-        ts = np.fromiter((int(round(float(t) * 1000.0)) for t, _ in vals), dtype=np.int64, count=len(vals))
-        v = np.fromiter((float(x) for _, x in vals), dtype=np.float64, count=len(vals))
+        if len(vals) == 0:
+            out.append((dict(item["metric"]), np.zeros(0, np.int64), np.zeros(0, np.float64)))
+            continue
+        cols = np.asarray(vals, dtype=object)
+        ts = np.rint(cols[:, 0].astype(np.float64) * 1000.0).astype(np.int64)
+        v = cols[:, 1].astype(str).astype(np.float64)          # numpy parses "NaN", "+Inf", "-Inf" as Prometheus writes them
         out.append((dict(item["metric"]), ts, v))
     return out
+
+
+def raw_series(labels: Dict[str, str], ts_ms, values) -> Tuple[Dict[str, str], np.ndarray, np.ndarray]:
+    """One series as a remote-read client holds it: int64 ms time stamps and fp64 values, no strings.
+    Stale markers keep their bit pattern (drop_stale removes them in build_irregular_batch); put such
+    tuples in a list where a query_range answer would go."""
+    return dict(labels), np.ascontiguousarray(ts_ms, dtype=np.int64), np.ascontiguousarray(values, dtype=np.float64)
 
 
 def _scalar_role(name: str, labels: Dict[str, str]) -> int:
@@ -88,9 +106,47 @@ class HostSeries:
         self.params, self.index, self.epoch_ms = params, index, epoch_ms
 
 
+class DuplicateBucketSeries(ValueError):
+    pass
+
+
+def _merge_bucket_series(group, what: str, aggregate: bool):
+    """`sum(rate(..._bucket[r])) by (le)` (mlflow_operator.py:367) adds the RATES of every series
+    that shares an `le` (replicas, extra labels).  The kernels take one counter row per `le`, so
+    several series with one `le` are refused by default; with aggregate=True they are added as
+    counters, which gives the same sum of rates only if they are scraped together and none of them
+    resets (then increase(a) + increase(b) = increase(a + b) up to one rounding); anything else is
+    refused."""
+    by_le: Dict[float, List[Tuple[np.ndarray, np.ndarray]]] = {}
+    for le, ts, v in group:
+        by_le.setdefault(le, []).append((ts, v))
+    out = []
+    for le in sorted(by_le):
+        series = by_le[le]
+        if len(series) > 1:
+            if not aggregate:
+                raise DuplicateBucketSeries(
+                    f"{what}: {len(series)} bucket series share le={le}; Prometheus would add their rates "
+                    "(sum by (le)).  Pass aggregate_buckets=True to add them as counters (same scrape times, "
+                    "no resets), or pre-aggregate.")
+            ts0 = series[0][0]
+            total = np.zeros(len(ts0), dtype=np.float64)
+            for ts, v in series:
+                if len(ts) != len(ts0) or not np.array_equal(ts, ts0):
+                    raise DuplicateBucketSeries(f"{what}: series sharing le={le} are scraped at different times")
+                if len(v) > 1 and np.any(np.diff(v) < 0):
+                    raise DuplicateBucketSeries(f"{what}: a series sharing le={le} has a counter reset; "
+                                                "its rate cannot be folded into a summed counter")
+                total = total + v
+            out.append((le, ts0, total))
+        else:
+            out.append((le, series[0][0], series[0][1]))
+    return out
+
+
 def build_host_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str, str], Tuple[str, str]],
                      period_ms: int = 15000, epoch_ms: Optional[int] = None, dtype: int = 0,
-                     **param_overrides) -> HostSeries:
+                     aggregate_buckets: bool = False, **param_overrides) -> HostSeries:
     """answers: {metric name: query_range answer}.  versions: {(deployment_name, namespace):
     (new predictor_name, old predictor_name)}.  Every (pair, version) must expose the same
     scalar label sets (same K, same roles in the same order after sorting by labels) and the
@@ -129,7 +185,7 @@ def build_host_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str, str
     T = max(len(ts) for ts in all_ts)
     roles_ref, le_ref = None, None
     K = max((len(g) for g in scal.values()), default=0)
-    B = max((len(g) for g in buck.values()), default=0)
+    B = max((len({it[0] for it in g}) for g in buck.values()), default=0)
     dt = np.float32 if dtype == 1 else np.float64
     scalars = np.zeros((n, 2, K, T), dtype=dt)
     buckets = np.zeros((n, 2, B, T), dtype=dt)
@@ -158,7 +214,7 @@ def build_host_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str, str
                 if p0 != ph:
                     raise IrregularSeries(f"{pairs[i]} v{v}: series of one target are scraped at different times")
                 scalars[i, v, k] = vals
-            hist = sorted(buck.get((i, v), []), key=lambda it: it[0])
+            hist = _merge_bucket_series(buck.get((i, v), []), f"pair {pairs[i]} version {v}", aggregate_buckets)
             if len(hist) != B:
                 raise ValueError(f"pair {pairs[i]} version {v}: {len(hist)} buckets, expected {B}")
             les = np.array([h[0] for h in hist], dtype=np.float64)
@@ -240,7 +296,12 @@ def build_irregular_batch(answers: Dict[str, Iterable], versions: Dict[Tuple[str
                 raise ValueError(f"{name}{labels}: time stamps are not strictly increasing")
             slot = (row_of[key], vk)
             if name == CLIENT_BUCKET:
-                buck.setdefault(_le_value(labels["le"]), {})[slot] = (ts, v)
+                per_le = buck.setdefault(_le_value(labels["le"]), {})
+                if slot in per_le:
+                    raise DuplicateBucketSeries(
+                        f"{key} {labels.get('predictor_name')}: several bucket series share le={labels['le']}; Prometheus "
+                        "would add their rates (sum by (le)); pre-aggregate them")
+                per_le[slot] = (ts, v)
             else:
                 order = ((SERVER_COUNT, CLIENT_SUM, CLIENT_COUNT).index(name), name,
                          tuple(sorted((k, x) for k, x in labels.items()

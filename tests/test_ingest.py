@@ -135,3 +135,43 @@ def test_stale_markers_are_not_samples():
     v = np.array([1.0, 2.0, stale, float("nan"), 5.0])
     t2, v2 = ingest.drop_stale(ts, v)
     assert list(t2) == [0, 15000, 45000, 60000] and math.isnan(v2[2]) and v2[3] == 5.0   # an ordinary NaN stays
+
+
+def test_two_label_sets_per_bucket_are_refused_or_summed():
+    """Real Seldon executors expose several series per `le` (replicas, extra labels); the reference's
+    query adds their rates (`sum(rate(..)) by (le)`, mlflow_operator.py:367).  Silently keeping one
+    of them would gate on one replica: the default is a clear error, the opt-in adds the counters."""
+    p = P.make_params(n_samples=48, n_buckets=6)
+    b = synth.generate(p, 3, seed=9, resets=False)
+    wire, versions, epoch = render(b)
+    doc = json.loads(wire[ingest.CLIENT_BUCKET])
+    extra = []
+    for item in doc["data"]["result"]:                       # a second replica with the same counts
+        extra.append({"metric": dict(item["metric"], replica="b"), "values": item["values"]})
+    doc["data"]["result"] += extra
+    wire2 = dict(wire)
+    wire2[ingest.CLIENT_BUCKET] = json.dumps(doc)
+    with pytest.raises(ingest.DuplicateBucketSeries, match="share le="):
+        ingest.build_host_batch(wire2, versions, period_ms=p.period_ms, epoch_ms=epoch)
+    host = ingest.build_host_batch(wire2, versions, period_ms=p.period_ms, epoch_ms=epoch, aggregate_buckets=True)
+    assert host.params.n_buckets == 6
+    assert np.array_equal(host.buckets[..., :48], 2.0 * b.buckets[..., :48])
+    with pytest.raises(ingest.DuplicateBucketSeries):
+        ingest.build_irregular_batch(wire2, versions, epoch_ms=epoch)
+    # a reset in one of the replicas cannot be folded into a summed counter
+    doc["data"]["result"][-1]["values"][10][1] = "0"
+    wire2[ingest.CLIENT_BUCKET] = json.dumps(doc)
+    with pytest.raises(ingest.DuplicateBucketSeries, match="reset"):
+        ingest.build_host_batch(wire2, versions, period_ms=p.period_ms, epoch_ms=epoch, aggregate_buckets=True)
+
+
+def test_raw_series_path_needs_no_strings():
+    """Remote-read shaped input (int64 ms + fp64 arrays) gives the same arrays as the JSON answers."""
+    p = P.make_params(n_samples=64, n_buckets=5)
+    b = synth.generate(p, 4, seed=13)
+    wire, versions, epoch = render(b)
+    raw = {name: [ingest.raw_series(lbl, ts, v) for lbl, ts, v in ingest.parse_matrix(ans)] for name, ans in wire.items()}
+    h1 = ingest.build_host_batch(wire, versions, period_ms=p.period_ms, epoch_ms=epoch)
+    h2 = ingest.build_host_batch(raw, versions, period_ms=p.period_ms, epoch_ms=epoch)
+    assert np.array_equal(h1.scalars, h2.scalars) and np.array_equal(h1.buckets, h2.buckets)
+    assert np.array_equal(h1.phase, h2.phase) and np.array_equal(h1.le, h2.le)
