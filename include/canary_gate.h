@@ -217,6 +217,19 @@ int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase
                   int64_t n_pairs, int64_t pair_offset, const cg_params* p, uint64_t seed,
                   double reset_prob, double adversarial, void* stream);
 
+/* Device-resident scrape history (the reference keeps none: every attempt asks Prometheus for
+ * "now", :302-303, and sleeps 10 s or 60 s in between, :340, :352; Prometheus' TSDB holds the
+ * hour).  Rows are allocated with slack after the newest sample (row_pitch > samples in use).
+ * cg_store_append writes one new scrape -- new_scalars [n_pairs][2][n_scalar], new_buckets
+ * [n_pairs][2][n_buckets], DEVICE memory, element type p->dtype -- into column `column` of every
+ * row.  cg_store_shift moves samples [shift, shift+count) of every row to [0, count) (the oldest
+ * `shift` samples fall off; count * element size <= 48 KB); the caller adds shift*period_ms to
+ * its phases.  Only p->dtype, n_scalar, n_buckets and row_pitch are used. */
+int cg_store_append(void* scalars, void* buckets, const void* new_scalars, const void* new_buckets,
+                    int64_t n_pairs, const cg_params* p, int32_t column, void* stream);
+int cg_store_shift(void* scalars, void* buckets, int64_t n_pairs, const cg_params* p, int32_t shift,
+                   int32_t count, void* stream);
+
 /* Same as cg_eval_fused with an explicit kernel choice: path 0 = automatic, 1 = the general
  * resident-tile kernel, 2 = the streaming kernel (CG_EINVAL if the geometry is not covered:
  * it needs window = 4 scrape periods and tick step = 2/3 period, the reference's constants

@@ -1,8 +1,9 @@
 """Import the UNMODIFIED reference operator under stub packages and drive its
 canary loop with a fake Prometheus and a virtual clock.
 
-TEST INFRASTRUCTURE ONLY (see oracle/pyoracle.py header).  Works only where
-/root/reference exists (the build container); the GPU box never runs this.
+TEST INFRASTRUCTURE ONLY (see oracle/pyoracle.py header).  Needs the reference's one
+Python file: /root/reference in the build container, or the untouched copy that
+`make -C oracle _ref` puts into oracle/_ref/ (git-ignored) so that the GPU box has it too.
 It is what pins decisions and traffic weights to the reference's own code:
 `get_model_metrics` (mlflow_operator.py:363-417), `should_promote_model`
 (:419-460) and the inline step loop of `create_or_update_seldon_deployment`
@@ -25,7 +26,20 @@ from typing import Callable, List, Optional
 
 from . import pyoracle
 
-REFERENCE_FILE = os.environ.get("CG_REFERENCE_FILE", "/root/reference/mlflow_operator.py")
+def _find_reference() -> str:
+    """The unmodified reference file: $CG_REFERENCE_FILE, else the read-only mount of the build
+    container, else the copy `make -C oracle _ref` (or __graft_entry__.build()) left in oracle/_ref/
+    (git-ignored; it travels to the GPU box with the snapshot, like the built .so files)."""
+    env = os.environ.get("CG_REFERENCE_FILE")
+    if env:
+        return env
+    mounted = "/root/reference/mlflow_operator.py"
+    if os.path.isfile(mounted):
+        return mounted
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "mlflow_operator.py")
+
+
+REFERENCE_FILE = _find_reference()
 
 
 def reference_available() -> bool:

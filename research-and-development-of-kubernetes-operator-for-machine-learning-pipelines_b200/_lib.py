@@ -38,6 +38,8 @@ def _load():
     lib.cg_stream_eligible.argtypes = [_vp]
     lib.cg_eval_irregular.argtypes = [_vp] * 9 + [_i64] + [_vp] * 6
     lib.cg_launch_info.argtypes = [_vp, _i64, _vp, _vp, _vp]
+    lib.cg_store_append.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, C.c_int32, _vp]
+    lib.cg_store_shift.argtypes = [_vp, _vp, _i64, _vp, C.c_int32, C.c_int32, _vp]
     if lib.cg_abi_version() != 1:
         raise ImportError("libcanarygate.so ABI version mismatch; rebuild")
     probe = CgParams()

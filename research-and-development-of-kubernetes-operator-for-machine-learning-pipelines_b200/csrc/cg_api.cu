@@ -13,6 +13,7 @@
 #include "cg_warp.cuh"
 #include "cg_irregular.cuh"
 #include "cg_synth.cuh"
+#include "cg_store.cuh"
 
 namespace {
 
@@ -507,6 +508,61 @@ int cg_synth_fill(void* scalars, void* buckets, const double* le, int32_t* phase
     else cg::synth_kernel<double><<<grid, 128, 0, (cudaStream_t)stream>>>(a);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "launch synth_kernel");
+    return CG_OK;
+}
+
+int cg_store_append(void* scalars, void* buckets, const void* new_scalars, const void* new_buckets,
+                    int64_t n_pairs, const cg_params* p, int32_t column, void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (column < 0 || column >= p->row_pitch) return fail(CG_EINVAL, "column %d outside the row (row_pitch %d)", column, p->row_pitch);
+    if (n_pairs == 0) return CG_OK;
+    if ((p->n_scalar && (!scalars || !new_scalars)) || (p->n_buckets && (!buckets || !new_buckets)))
+        return fail(CG_EINVAL, "NULL argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    for (int part = 0; part < 2; ++part) {
+        const int64_t n_series = n_pairs * 2 * (part ? p->n_buckets : p->n_scalar);
+        if (n_series == 0) continue;
+        void* rows = part ? buckets : scalars;
+        const void* fresh = part ? new_buckets : new_scalars;
+        const int grid = grid_for(n_series, 256);
+        if (p->dtype == CG_F32)
+            cg::store_append_kernel<float><<<grid, 256, 0, s>>>((float*)rows, (const float*)fresh, n_series, p->row_pitch, column);
+        else
+            cg::store_append_kernel<double><<<grid, 256, 0, s>>>((double*)rows, (const double*)fresh, n_series, p->row_pitch, column);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "launch store_append_kernel");
+        g_launches.fetch_add(1);
+    }
+    return CG_OK;
+}
+
+int cg_store_shift(void* scalars, void* buckets, int64_t n_pairs, const cg_params* p, int32_t shift, int32_t count,
+                   void* stream) {
+    int rc = check_params(p);
+    if (rc) return rc;
+    if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
+    if (shift < 0 || count < 0 || (int64_t)shift + count > p->row_pitch)
+        return fail(CG_EINVAL, "shift %d + count %d exceed the row (row_pitch %d)", shift, count, p->row_pitch);
+    if (n_pairs == 0 || shift == 0 || count == 0) return CG_OK;
+    const size_t smem = (size_t)count * elem_size(p);
+    if (smem > 48 * 1024) return fail(CG_EINVAL, "count %d: a row segment of more than 48 KB cannot be staged", count);
+    cudaStream_t s = (cudaStream_t)stream;
+    for (int part = 0; part < 2; ++part) {
+        const int64_t n_rows = n_pairs * 2 * (part ? p->n_buckets : p->n_scalar);
+        void* rows = part ? buckets : scalars;
+        if (n_rows == 0) continue;
+        if (!rows) return fail(CG_EINVAL, "NULL argument");
+        int64_t g = n_rows < 148 * 16 ? n_rows : 148 * 16;
+        if (p->dtype == CG_F32)
+            cg::store_shift_kernel<float><<<(int)g, 128, smem, s>>>((float*)rows, n_rows, p->row_pitch, shift, count);
+        else
+            cg::store_shift_kernel<double><<<(int)g, 128, smem, s>>>((double*)rows, n_rows, p->row_pitch, shift, count);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "launch store_shift_kernel");
+        g_launches.fetch_add(1);
+    }
     return CG_OK;
 }
 

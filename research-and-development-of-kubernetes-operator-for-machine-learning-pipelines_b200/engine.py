@@ -251,3 +251,104 @@ class HostPipeline:
         cur.wait_stream(self.compute_stream)
         self.compute_stream.synchronize()
         return out_h
+
+
+class RollingStore:
+    """Device-resident scrape history that grows one scrape at a time.
+
+    The reference re-asks Prometheus for "now" on every attempt (mlflow_operator.py:302-303) and
+    sleeps 10 s or 60 s in between (:340, :352); what changes between two attempts is one scrape
+    per series, not the hour.  Here the hour stays in HBM: `append_scrape` moves one value per
+    series over PCIe and `evaluate` runs the canary over the newest `p.n_samples` samples.
+
+    Rows have `slack` spare columns after the newest sample; when they are used up every row is
+    moved left once (cg_store_shift), so the amortised cost of an append is one column write.
+    Times are relative to column 0: `phase[n, 2]` is the scrape offset of each target within a
+    period and does not change; the tick grid follows the newest samples.
+    """
+
+    def __init__(self, p: CgParams, n_pairs: int, le: torch.Tensor, slack: int = 64, device=None):
+        self.dev = le.device if device is None else torch.device(device)
+        self.p, self.n, self.le = p.copy(), int(n_pairs), le
+        self.T = p.n_samples
+        esz = p.elem_bytes
+        self.align = 16 // esz                                   # samples per 16 bytes: bulk copies start on 16-byte boundaries
+        cap = self.T + max(int(slack), self.align)
+        self.cap = -(-cap // self.align) * self.align
+        dt = _elem_dtype(p)
+        K, B = p.n_scalar, p.n_buckets
+        # one spare row at the end: a view that starts `offset` samples into the rows is read row by row
+        self._sc = torch.zeros(self.n * 2 * K * self.cap + self.cap, dtype=dt, device=self.dev)
+        self._bk = torch.zeros(self.n * 2 * B * self.cap + self.cap, dtype=dt, device=self.dev)
+        self.scalars = self._sc[: self.n * 2 * K * self.cap].view(self.n, 2, K, self.cap)
+        self.buckets = self._bk[: self.n * 2 * B * self.cap].view(self.n, 2, B, self.cap)
+        self.phase = torch.zeros((self.n, 2), dtype=torch.int32, device=self.dev)
+        self._new_sc = torch.empty((self.n, 2, K), dtype=dt, device=self.dev)
+        self._new_bk = torch.empty((self.n, 2, B), dtype=dt, device=self.dev)
+        self._phase_eff = torch.empty_like(self.phase)
+        self.count = 0
+        self.h2d_bytes = 0
+        self._pp = p.copy()
+        self._pp.row_pitch = self.cap
+
+    def load(self, scalars: torch.Tensor, buckets: torch.Tensor, phase: torch.Tensor):
+        """Bulk start: device tensors [n, 2, K|B, m] with m <= capacity samples, and the phases."""
+        m = scalars.shape[-1] if self.p.n_scalar else buckets.shape[-1]
+        if m > self.cap:
+            raise ValueError("more samples than the store holds")
+        if self.p.n_scalar:
+            self.scalars[..., :m].copy_(scalars)
+        if self.p.n_buckets:
+            self.buckets[..., :m].copy_(buckets)
+        self.phase.copy_(phase)
+        self.count = m
+
+    def append_scrape(self, new_scalars: torch.Tensor, new_buckets: torch.Tensor):
+        """One new scrape of every series: [n, 2, K] and [n, 2, B], pinned host or device memory."""
+        p = self._pp
+        if self.count == self.cap:                               # slack used up: the oldest samples fall off
+            keep = self.T - 1
+            _lib.check(_lib.lib.cg_store_shift(_ptr(self.scalars if p.n_scalar else None),
+                                               _ptr(self.buckets if p.n_buckets else None), self.n, C.byref(p),
+                                               self.count - keep, keep, _stream_ptr()), "cg_store_shift")
+            self.count = keep
+        self.h2d_bytes = 0
+        for src, dst in ((new_scalars, self._new_sc), (new_buckets, self._new_bk)):
+            if dst.numel():
+                dst.copy_(src, non_blocking=True)
+                if not src.is_cuda:
+                    self.h2d_bytes += src.numel() * src.element_size()
+        _lib.check(_lib.lib.cg_store_append(_ptr(self.scalars if p.n_scalar else None),
+                                            _ptr(self.buckets if p.n_buckets else None),
+                                            _ptr(self._new_sc if p.n_scalar else None),
+                                            _ptr(self._new_bk if p.n_buckets else None), self.n, C.byref(p),
+                                            self.count, _stream_ptr()), "cg_store_append")
+        self.count += 1
+
+    def view(self):
+        """What `evaluate` hands to the kernels: (first column, samples in view, params, tick0 shift in
+        periods).  The view starts on a 16-byte boundary at or before the newest T samples."""
+        first = max(0, self.count - self.T)
+        off = first - first % self.align
+        pp = self._pp.copy()
+        pp.n_samples = self.count - off
+        pp.tick0_ms = self.p.tick0_ms + first * self.p.period_ms
+        return off, self.count - off, pp, first
+
+    def evaluate(self, out: Optional[torch.Tensor] = None, has_previous=None, start_tick=None, want_bits: bool = False):
+        """The whole canary (metrics on the dense tick grid -> gate -> step loop) over the newest
+        samples of every pair.  -> decisions [n, 6] int32 (and the gate bits)."""
+        if self.count < 2:
+            raise ValueError("fewer than two scrapes in the store")
+        off, _, pp, _ = self.view()
+        esz = pp.elem_bytes
+        torch.add(self.phase, off * pp.period_ms, out=self._phase_eff)
+        dec = out if out is not None else torch.empty((self.n, 6), dtype=torch.int32, device=self.dev)
+        _want(dec, torch.int32, "decisions")
+        bits = torch.empty((self.n, pp.n_words), dtype=torch.int32, device=self.dev) if want_bits else None
+        sc = C.c_void_p(self.scalars.data_ptr() + off * esz) if pp.n_scalar else None
+        bk = C.c_void_p(self.buckets.data_ptr() + off * esz) if pp.n_buckets else None
+        _lib.check(_lib.lib.cg_eval_fused(sc, bk, _ptr(self.le if pp.n_buckets else None), _ptr(self._phase_eff),
+                                          _ptr(has_previous), _ptr(start_tick), self.n, C.byref(pp), _ptr(dec),
+                                          _ptr(bits), None, None, _stream_ptr()), "cg_eval_fused")
+        return (dec, bits) if want_bits else dec

@@ -1,5 +1,5 @@
-"""Live check (build container only): the oracles under the UNMODIFIED reference.
-Skipped where /root/reference is absent (the GPU box)."""
+"""Live check: the oracles under the UNMODIFIED reference.
+Runs wherever the reference file is: /root/reference in the build container, or its untouched copy in oracle/_ref/ (made by `make -C oracle _ref`, git-ignored, shipped to the GPU box with the snapshot)."""
 import math
 
 import numpy as np
@@ -9,7 +9,7 @@ import canary_b200  # noqa: F401
 from canary_b200 import params as P, synth
 from oracle import c_oracle as co, ref_loader as rl, soa_bridge as sb
 
-pytestmark = pytest.mark.skipif(not rl.reference_available(), reason="no /root/reference here")
+pytestmark = pytest.mark.skipif(not rl.reference_available(), reason="no reference file (run make -C oracle _ref where /root/reference is mounted)")
 
 
 def test_reference_imports_unmodified():
