@@ -184,7 +184,10 @@ CG_DEVINL LaneGeo lane_setup(const WarpArgs& a, const SlotGeom& g, int lane, int
                              unsigned& valid_ticks) {
     LaneGeo lg;
     const int b = g.i00 + 2 * kG * lane;
-    const int lim = (a.p.n_samples - kTile) & ~1;
+    // The tile starts on an even sample and lies inside the ROW; with an odd number of samples its
+    // last sample may be the one just after the series (the pitch is even, so it exists): windows
+    // that would use it host no tick, and a reset seen against it only costs a needless correction.
+    const int lim = (a.p.n_samples - kTile + 1) & ~1;
     int bt = b < 0 ? 0 : b;
     if (bt > lim) bt = lim;
     lg.bt = bt; lg.dl = b - bt; lg.act = 0u; lg.host = 0u;
@@ -199,7 +202,7 @@ CG_DEVINL LaneGeo lane_setup(const WarpArgs& a, const SlotGeom& g, int lane, int
             const int tt = 3 * kk + s, j = tick_base + tt, k = 2 * kk + c;
             if (j >= chunk0 && j < chunk_end) {
                 valid_ticks |= 1u << tt;
-                if (n4 && k >= 0 && k < kLaneWin) { lg.act |= 1u << tt; lg.host |= 1u << k; }
+                if (n4 && k >= 0 && k < kLaneWin && bt + k + 3 < a.p.n_samples) { lg.act |= 1u << tt; lg.host |= 1u << k; }
             }
         }
     }
