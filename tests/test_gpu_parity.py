@@ -262,3 +262,22 @@ def test_host_pipeline_matches_device_path():
         assert np.array_equal(out.numpy(), want)
     assert pipe.h2d_bytes == b.scalars.nbytes + b.buckets.nbytes + b.phase.nbytes
     assert pipe.d2h_bytes == 300 * 24
+
+
+def test_metric_values_at_scale_8192_pairs():
+    """Metric VALUES (not only decisions) on 8,192 pairs of BASELINE.json configs[3], from the device
+    generator: every rate / quantile / ratio of the streaming kernel's dense grid against the C oracle,
+    bit for bit (required bar 1e-6 relative), plus validity bytes, gate bits and decisions."""
+    p = P.make_params()
+    n = 8192
+    le = torch.from_numpy(synth.default_le(p.n_buckets)).cuda()
+    sc, bk, ph = engine.synth_fill(n, p, le, seed=0xC0FFEE + 3, adversarial=0.01)
+    dec, bits, m, v = engine.eval_fused(sc, bk, le, ph, p, want_bits=True, want_metrics=True, path=2)
+    torch.cuda.synchronize()
+    h = [t.cpu().numpy() for t in (sc, bk, ph)]
+    le_h = le.cpu().numpy()
+    want_m, want_v = co.eval_grid(h[0], h[1], le_h, h[2], p, n_threads=co.max_threads())
+    assert_metrics_match(m.cpu().numpy(), want_m, v.cpu().numpy(), want_v, rtol=1e-6, exact=True, what="8192 pairs")
+    want_dec, want_bits = co.eval_fused(h[0], h[1], le_h, h[2], p, n_threads=co.max_threads())
+    assert np.array_equal(bits.cpu().numpy().view(np.uint32), want_bits)
+    assert np.array_equal(dec.cpu().numpy(), want_dec)
