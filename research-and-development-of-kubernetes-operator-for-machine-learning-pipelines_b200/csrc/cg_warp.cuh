@@ -3,33 +3,39 @@
 // with Prometheus' usual 15 s scrapes).
 //
 // Layout of the work
-//   * One WARP owns one model pair and streams its series rows through a private shared-memory
-//     ring filled by the TMA bulk-copy engine (cp.async.bulk + mbarrier complete_tx).  The warp
-//     is its own producer: after the last lane is done with a slot, lane 0 issues the copy that
-//     comes n_slots later.  No CTA barrier, no cross-warp traffic: a CTA is one warp.
-//     Row order per pair: scalar rows of the new version, scalar rows of the old version, then
-//     per version the +Inf bucket row followed by bucket rows 0..B-2.  Every sample leaves HBM
-//     once.
-//   * A lane owns 12 consecutive ticks = 4 periods of the tick grid (3 tick steps = 2 scrape
-//     periods exactly), whose 4-sample windows start at 9 consecutive samples: one 12-sample
-//     register tile per row (six 128-bit shared loads), 9 window deltas.  30 lanes cover the
-//     355 ticks of an hour.
+//   * One CTA = the kWarps (two) warps of one model pair; 8 CTAs per SM; persistent over pairs.
+//     The pair's series rows stream through the CTA's shared-memory ring, filled by the TMA
+//     bulk-copy engine (cp.async.bulk + mbarrier complete_tx, 2 rows = 3.8 KB per copy).  The CTA
+//     is its own producer: when both warps are done with a slot, thread 0 issues the copy that
+//     comes n_slots later (a per-pass table in shared memory says which rows).  Row order per
+//     pair: scalar rows of the new version, scalar rows of the old version, then per version the
+//     +Inf bucket row followed by bucket rows 0..B-2.  Every sample leaves HBM once.
+//   * A lane owns kG = 2 periods of the tick grid = 6 consecutive ticks (3 tick steps are exactly
+//     2 scrape periods), whose 4-sample windows start at 5 consecutive samples: one 8-sample
+//     register tile per row (four 128-bit shared loads), 5 window deltas.  60 of the pair's 64
+//     lanes cover the 355 ticks of an hour; longer grids take more passes over the rows.  The
+//     tick grid is rotated by 0..2 ticks per (pair, version) so that tiles start on even samples,
+//     and edge lanes slide their tile back inside the series.
 //   * Bucket rows are processed in WINDOW space.  A tick's increase is delta * f with f > 0
 //     depending on the tick alone, and x -> fl(fl(x*f)/range) is monotone, so the monotonic fix
-//     of histogram_quantile is a running max of window deltas (one DMNMX per window and row) and
-//     "this bucket reaches the rank" is a compare of the delta against a per-window threshold
-//     (an under-estimate, so it never misses).  Only when a compare fires is anything evaluated
-//     per tick, exactly, in rate space, by an event loop over the flagged windows; it captures
-//     the interpolated quantile on the spot.
+//     of histogram_quantile is a running max of window deltas (one compare-select per window and
+//     row) and "this bucket reaches the rank" is a compare of the delta against a per-window
+//     threshold (an under-estimate, so it never misses).  Only when a compare fires is anything
+//     evaluated per tick, exactly, in rate space, by an event loop over the flagged windows; it
+//     captures the interpolated quantile on the spot and, for the old version, decides the
+//     quantile part of the gate against the new version's value.
 //   * Counter resets are corrected branch-free in the register tile when any lane sees one.  The
 //     zero-point clamp of extrapolatedRate makes a row's factor tick- and row-specific: one
-//     multiply per tile proves it cannot fire; rows where it does are excluded from the window
+//     multiply per tile proves it cannot fire; rows where it does are kept out of the window
 //     running max and folded, exactly, into a per-tick rate-space maximum kept in shared memory.
-//   * Scalar rows (sum(increase(...)) per role) are evaluated per tick from the same window
-//     deltas; the two versions' ratios are compared as soon as the old version's scalar rows are
-//     through, so only pass/fail bits wait for the quantiles.
+//   * Scalar rows (sum(increase(...)) per role): all K rows of a version are resident in the ring
+//     at once and each lane walks its ticks over them with five running sums; the two versions'
+//     ratios are compared as soon as the old version's scalar rows are through, so only pass/fail
+//     bits wait for the quantiles.
+//   * Divisions: by constants with the 3-operation Markstein sequence, by data with a Newton
+//     sequence that is proven (tests/div_check.cpp) to give the correctly rounded quotient.
 //   * Ticks the fast path cannot decide exactly (series edges, a sample on a window edge, a
-//     non-finite sample, a mis-speculated observation count) are re-evaluated at the end by the
+//     non-finite sample, a mis-speculated observation count) are re-evaluated at the end by a
 //     whole warp from global memory with the plain sequential semantics (coop_eval_tick).
 //     Results are bit-identical to the oracle either way.
 //
