@@ -39,6 +39,8 @@ def _units():
         for nq in (1, 2, 3, 4):
             name = f"cg_launch_warp_{tchar}{nq}"
             defs = [f"-DCG_INST_T={tname}", f"-DCG_INST_NQ={nq}", f"-DCG_INST_NAME={name}"] + extra
+            if os.environ.get("CG_CHECKED"):                 # developer build: our own bounds checks (tools/run_checked.py)
+                defs += ["-DCG_CHECKED"] + (["-DCG_CHECK_EXPORT"] if name == "cg_launch_warp_d1" else [])
             units.append((name, "cg_warp_inst.cu", defs))
     return units
 

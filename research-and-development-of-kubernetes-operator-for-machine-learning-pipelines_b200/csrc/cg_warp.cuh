@@ -70,6 +70,16 @@ constexpr int kChunkTicks = 382;           // ticks one pass over the rows cover
 constexpr int kRowsPerUse = CG_ROWS_PER_USE;   // rows per ring slot
 constexpr unsigned kFullMask = 0xffffffffu;
 
+// Developer build with bounds checks of our own (build.py with CG_CHECKED=1; tools/run_checked.py reads the
+// counters): every shared-memory tile, ring fill and bit-vector word the kernel touches is tested against its
+// array; a failed test bumps a counter instead of touching memory it should not.
+#if defined(CG_CHECKED) && defined(__CUDACC__)
+static __device__ unsigned int cg_check_failures[8];
+#define CG_CHECK(i, cond) do { if (!(cond)) atomicAdd(&cg_check_failures[i], 1u); } while (0)
+#else
+#define CG_CHECK(i, cond)
+#endif
+
 #ifndef __CUDACC__
 // host emulation only: what a lane's last bucket row did (warp-level statistics in tests/host_emul)
 struct EmulRowStat { int reset, event, windows, captures, clamps, cfl, hfl; };
@@ -861,6 +871,9 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         const FillEntry e = s_tab[c.u];
         const char* src = ((e.meta >> 31) ? c.bk : c.sc) + e.off;
         const uint32_t bytes = e.meta & 0x7fffffffu;
+        CG_CHECK(0, c.u >= 0 && c.u < a.uses_per_pass && slot < (uint32_t)n_slots && bytes <= a.slot_bytes && bytes % 16 == 0);
+        CG_CHECK(1, (e.meta >> 31) ? (src >= (const char*)a.buckets && src + bytes <= (const char*)a.buckets + a.n_pairs * pair_bytes_bk)
+                                   : (src >= (const char*)a.scalars && src + bytes <= (const char*)a.scalars + a.n_pairs * pair_bytes_sc));
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // reads of the slot before the async write
         mbar_arrive_expect_tx(bars + slot, bytes);
         bulk_g2s(smem + (size_t)slot * a.slot_bytes, src, bytes, bars + slot);
@@ -911,6 +924,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 unsigned vt;
                 lg[ver] = lane_setup(a, geo[ver], tid, chunk0, chunk_end, vt);
                 fbm[ver] = vt & ~lg[ver].act;
+                CG_CHECK(3, lg[ver].bt >= 0 && lg[ver].bt + kTile <= pitch && !(lg[ver].bt & 1) && !(lg[ver].act & ~vt));
             }
 
             // ---- scalar rows of both versions: all K rows of a version resident, then released together
@@ -921,6 +935,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 auto row_ptr = [&](int r) -> const T* {
                     uint32_t s = h + (uint32_t)(r / kRowsPerUse);
                     if (s >= (uint32_t)n_slots) s -= n_slots;
+                    CG_CHECK(2, r >= 0 && r < p.n_scalar && s < (uint32_t)n_slots);
                     return reinterpret_cast<const T*>(smem + (size_t)s * a.slot_bytes) + (r % kRowsPerUse) * pitch;
                 };
                 scalar_phase<T>(a, geo[ver], lg[ver], L, ver, pair * 2 + ver, geo[ver].j0 + kLaneTicks * tid, delta,
@@ -953,9 +968,13 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                         const T* rows = slot_wait(0);
                         const int first = u * kRowsPerUse, nr = min(kRowsPerUse, B - 1 - first);
 #pragma unroll 1
-                        for (int r = 0; r < nr; ++r)
+                        for (int r = 0; r < nr; ++r) {
+                            CG_CHECK(4, (const unsigned char*)(rows + r * pitch + l.bt) >= smem &&
+                                        (const unsigned char*)(rows + r * pitch + l.bt + kTile) <= smem + (size_t)n_slots * a.slot_bytes &&
+                                        first + r < B - 1);
                             bucket_row<T, NQ>(a, g, l, L, rows + r * pitch + l.bt, first + r, ver, delta, pv, tick_base,
                                               prevw, ymin, found, fb, pass_q, any);
+                        }
                         pair_sync();
                         slot_release();
                     }
@@ -974,11 +993,13 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
             // ---- this pass's bits: promote bits from the old version's lanes, fallback ticks from both
             {
                 const BitField pb = place_bits(pass_sc & pass_q & act_old, geo[1].j0 + kLaneTicks * tid);
+                CG_CHECK(5, (!pb.lo || (pb.word0 >= 0 && pb.word0 < n_words)) && (!pb.hi || pb.word0 + 1 < n_words));
                 if (pb.lo) atomicOr(s_bits + pb.word0, pb.lo);
                 if (pb.hi) atomicOr(s_bits + pb.word0 + 1, pb.hi);
 #pragma unroll
                 for (int ver = 0; ver < 2; ++ver) {
                     const BitField f = place_bits(fbm[ver], geo[ver].j0 + kLaneTicks * tid);
+                    CG_CHECK(6, (!f.lo || (f.word0 >= 0 && f.word0 < n_words)) && (!f.hi || f.word0 + 1 < n_words));
                     if (f.lo) atomicOr(s_fb + f.word0, f.lo);
                     if (f.hi) atomicOr(s_fb + f.word0 + 1, f.hi);
                 }

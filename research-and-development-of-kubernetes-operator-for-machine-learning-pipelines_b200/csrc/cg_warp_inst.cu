@@ -7,3 +7,12 @@
 cudaError_t CG_INST_NAME(const cg::WarpArgs& a, int grid, cudaStream_t s) {
     return cg::launch_warp_tn<CG_INST_T, CG_INST_NQ>(a, grid, s);
 }
+
+#if defined(CG_CHECKED) && defined(CG_CHECK_EXPORT)
+// developer build only (see CG_CHECK in cg_warp.cuh): failed bounds checks of THIS instance since the last reset
+extern "C" int cg_debug_check_failures(unsigned int* out8, int reset) {
+    if (cudaMemcpyFromSymbol(out8, cg::cg_check_failures, sizeof(unsigned int) * 8) != cudaSuccess) return 1;
+    if (reset) { unsigned int z[8] = {0}; cudaMemcpyToSymbol(cg::cg_check_failures, z, sizeof(z)); }
+    return 0;
+}
+#endif
