@@ -30,3 +30,5 @@ print(f"{src}: pairs {n} warp-rows {rows}  reset_rows {c[3] / rows:.3f}  event_r
 d = np.diff(b.buckets[:, :, :, :p.n_samples], axis=-1)
 print("resets per bucket row:", float((d < 0).sum()) / (n * 2 * p.n_buckets), " first sample median", float(np.median(b.buckets[..., 0])),
       " min", float(b.buckets[..., 0].min()))
+print(f"warp-rows with a clamp flag {c[8] / rows:.3f}  with a threshold flag {c[9] / rows:.3f}  warp-level event iterations per pair {c[4] / n:.0f}  "
+      f"lane-windows per pair {c[7] / n:.0f}  clamped lane-windows per pair {c[6] / n:.0f}")
