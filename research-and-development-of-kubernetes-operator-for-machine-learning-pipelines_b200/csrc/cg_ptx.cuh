@@ -51,4 +51,29 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
         : "memory");
 }
 
+// The same with 32-bit shared-memory addresses the caller keeps in registers.
+__device__ __forceinline__ void mbar_arrive_expect_tx_s(uint32_t bar_s, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait_s(uint32_t bar_s, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar_s), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+__device__ __forceinline__ void bulk_g2s_s(uint32_t dst_s, const void* gmem_src, uint32_t bytes, uint32_t bar_s) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s),
+        "l"(gmem_src), "r"(bytes), "r"(bar_s)
+        : "memory");
+}
+
 }  // namespace cg

@@ -260,6 +260,23 @@ CG_DEVINL QuantConst quant_const(const WarpArgs& a) {
     return c;
 }
 
+// ---- a position in a series row ----------------------------------------------------------
+// On the device the rows sit in the shared-memory ring: the position is a 32-bit shared-memory
+// address, so that moving along a row or to the next row is one integer add.  The host emulation
+// reads the caller's arrays through a plain pointer.
+template <typename T> struct Row {
+#ifdef __CUDACC__
+    uint32_t s;
+    __device__ __forceinline__ Row operator+(int n) const { return Row{s + (uint32_t)(n * (int)sizeof(T))}; }
+    __device__ __forceinline__ const T* ptr() const { return reinterpret_cast<const T*>(__cvta_shared_to_generic((size_t)s)); }
+#else
+    const T* p;
+    Row(const T* q) : p(q) {}
+    Row operator+(int n) const { return Row(p + n); }
+    const T* ptr() const { return p; }
+#endif
+};
+
 // ---- register tile ---------------------------------------------------------------------
 template <typename T> struct TileLoad;
 template <> struct TileLoad<double> {
@@ -323,7 +340,8 @@ CG_DEVINL double pick_window(const double (&v)[kLaneWin], int k) {
 
 // Appendix A step 2 for the 4 samples at t4; also returns the first sample
 template <typename T>
-CG_DEVINL double window4(const T* __restrict__ t4, double& first) {
+CG_DEVINL double window4(const Row<T> w4, double& first) {
+    const T* __restrict__ t4 = w4.ptr();
     const double x0 = (double)t4[0], x1 = (double)t4[1], x2 = (double)t4[2], x3 = (double)t4[3];
     double res = x3 - x0;
     if (x1 < x0) res += x0;
@@ -456,7 +474,7 @@ CG_DEVINL void gate_quantile_known(const WarpArgs& a, const Lane& L, int ver, in
 // Speculates that the +Inf bucket holds the observations (checked in bucket_finish).
 template <typename T, int NQ>
 CG_DEVINL void inf_row_setup(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                             const QuantConst& qc, const T* __restrict__ tile, int ver, int delta, int64_t pv,
+                             const QuantConst& qc, const Row<T> tile, int ver, int delta, int64_t pv,
                              int tick_base, uint64_t& found, unsigned& fb, unsigned& pass_bits) {
     const cg_params& p = a.p;
     const int W = p.n_q + CG_M_EXTRA;
@@ -509,7 +527,7 @@ CG_DEVNOINL double interpolate_quantile(const double* __restrict__ le, int b, do
 // instead).
 template <typename T, int NQ>
 CG_DEVINL unsigned bucket_events(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                                 const T* __restrict__ tile, int b, unsigned mask, const double (&prevw)[kLaneWin],
+                                 const Row<T> tile, int b, unsigned mask, const double (&prevw)[kLaneWin],
                                  int ver, int delta, int64_t pv, int tick_base, uint64_t& found, unsigned& fb,
                                  unsigned& pass_bits) {
     const cg_params& p = a.p;
@@ -604,11 +622,11 @@ CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, 
 // ymin = smallest delta that may reach a rank still searched
 template <typename T, int NQ, typename AnyFn>
 CG_DEVINL void bucket_row(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L,
-                          const T* __restrict__ tile, int b, int ver, int delta, int64_t pv, int tick_base,
+                          const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
                           double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
                           unsigned& pass_bits, AnyFn any) {
     double x[kTile], w[kLaneWin];
-    TileLoad<T>::load(tile, x);
+    TileLoad<T>::load(tile.ptr(), x);
     window_deltas(x, w);
     const double gmin = g.gmin;
     bool cflag;
@@ -843,7 +861,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
     L.lane = tid;
     L.st = reinterpret_cast<double*>(smem + a.off_state) + tid;
     L.sa = reinterpret_cast<double*>(smem + a.off_scratch) + tid;
-    const int B = p.n_buckets, W = p.n_q + CG_M_EXTRA, pitch = p.row_pitch;
+    const int B = p.n_buckets, W = p.n_q + CG_M_EXTRA;
     const int n_sc = a.n_sc_uses, n_bk = a.n_bk_uses, n_slots = a.n_slots;
     const WarpAny any;
     if (tid == 0) {
@@ -867,35 +885,42 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
             if (++c.chunk == a.n_chunks) { c.chunk = 0; c.pair += gridDim.x; skip_pairs(c); }
         }
     };
-    auto issue_fill = [&](const FillCursor& c, uint32_t slot) {      // one thread
+    const uint32_t ring_s = smem_u32(smem), bars_s = ring_s + a.off_bars;   // the ring sits at offset 0
+    auto issue_fill = [&](const FillCursor& c, uint32_t slot_s, uint32_t bar_s) {      // one thread
         const FillEntry e = s_tab[c.u];
         const char* src = ((e.meta >> 31) ? c.bk : c.sc) + e.off;
         const uint32_t bytes = e.meta & 0x7fffffffu;
-        CG_CHECK(0, c.u >= 0 && c.u < a.uses_per_pass && slot < (uint32_t)n_slots && bytes <= a.slot_bytes && bytes % 16 == 0);
+        CG_CHECK(0, c.u >= 0 && c.u < a.uses_per_pass && slot_s - ring_s < (uint32_t)n_slots * a.slot_bytes && bytes <= a.slot_bytes && bytes % 16 == 0);
         CG_CHECK(1, (e.meta >> 31) ? (src >= (const char*)a.buckets && src + bytes <= (const char*)a.buckets + a.n_pairs * pair_bytes_bk)
                                    : (src >= (const char*)a.scalars && src + bytes <= (const char*)a.scalars + a.n_pairs * pair_bytes_sc));
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // reads of the slot before the async write
-        mbar_arrive_expect_tx(bars + slot, bytes);
-        bulk_g2s(smem + (size_t)slot * a.slot_bytes, src, bytes, bars + slot);
+        mbar_arrive_expect_tx_s(bar_s, bytes);
+        bulk_g2s_s(slot_s, src, bytes, bar_s);
     };
     FillCursor fill;
     fill.pair = blockIdx.x; fill.chunk = 0; fill.u = 0;
     skip_pairs(fill);
     for (int s = 0; s < n_slots; ++s) {          // prologue: fill the whole ring
-        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, (uint32_t)s);
+        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, ring_s + (uint32_t)s * a.slot_bytes, bars_s + 8u * (uint32_t)s);
         cursor_next(fill);
     }
-    uint32_t head = 0, head_parity = 0;           // oldest slot in use and the parity of its mbarrier
-    auto slot_wait = [&](int i) -> const T* {     // i-th slot from the head
+    // oldest slot in use: index, shared addresses of its rows and of its mbarrier, parity of that mbarrier
+    uint32_t head = 0, head_parity = 0, head_s = ring_s, head_bar = bars_s;
+    auto slot_wait = [&](int i) -> uint32_t {     // i-th slot from the head; returns the shared address of its rows
         uint32_t s = head + (uint32_t)i, par = head_parity;
         if (s >= (uint32_t)n_slots) { s -= n_slots; par ^= 1u; }
-        mbar_wait(bars + s, par);
-        return reinterpret_cast<const T*>(smem + (size_t)s * a.slot_bytes);
+        mbar_wait_s(bars_s + 8u * s, par);
+        return ring_s + s * a.slot_bytes;
+    };
+    auto head_wait = [&]() -> uint32_t {
+        mbar_wait_s(head_bar, head_parity);
+        return head_s;
     };
     auto slot_release = [&]() {                   // the head slot; callers have synchronised the pair's warps
-        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, head);
+        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, head_s, head_bar);
         cursor_next(fill);
-        if (++head == (uint32_t)n_slots) { head = 0; head_parity ^= 1u; }
+        head_s += a.slot_bytes; head_bar += 8u;
+        if (++head == (uint32_t)n_slots) { head = 0; head_parity ^= 1u; head_s = ring_s; head_bar = bars_s; }
     };
 
     for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
@@ -924,7 +949,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                 unsigned vt;
                 lg[ver] = lane_setup(a, geo[ver], tid, chunk0, chunk_end, vt);
                 fbm[ver] = vt & ~lg[ver].act;
-                CG_CHECK(3, lg[ver].bt >= 0 && lg[ver].bt + kTile <= pitch && !(lg[ver].bt & 1) && !(lg[ver].act & ~vt));
+                CG_CHECK(3, lg[ver].bt >= 0 && lg[ver].bt + kTile <= p.row_pitch && !(lg[ver].bt & 1) && !(lg[ver].act & ~vt));
             }
 
             // ---- scalar rows of both versions: all K rows of a version resident, then released together
@@ -932,11 +957,11 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
             for (int ver = 0; ver < 2; ++ver) {
                 for (int i = 0; i < n_sc; ++i) slot_wait(i);
                 const uint32_t h = head;
-                auto row_ptr = [&](int r) -> const T* {
+                auto row_ptr = [&](int r) -> Row<T> {
                     uint32_t s = h + (uint32_t)(r / kRowsPerUse);
                     if (s >= (uint32_t)n_slots) s -= n_slots;
                     CG_CHECK(2, r >= 0 && r < p.n_scalar && s < (uint32_t)n_slots);
-                    return reinterpret_cast<const T*>(smem + (size_t)s * a.slot_bytes) + (r % kRowsPerUse) * pitch;
+                    return Row<T>{ring_s + s * a.slot_bytes + (uint32_t)(r % kRowsPerUse) * a.row_bytes};
                 };
                 scalar_phase<T>(a, geo[ver], lg[ver], L, ver, pair * 2 + ver, geo[ver].j0 + kLaneTicks * tid, delta,
                                 row_ptr, pass_sc);
@@ -955,9 +980,10 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     unsigned fb = fbm[ver];
                     double prevw[kLaneWin], ymin[kLaneWin];
                     uint64_t found = ~0ull;
+                    const uint32_t tile_off = (uint32_t)l.bt * (uint32_t)sizeof(T);
                     {
-                        const T* rows = slot_wait(0);
-                        inf_row_setup<T, NQ>(a, g, l, L, qc, rows + l.bt, ver, delta, pv, tick_base, found, fb, pass_q);
+                        const Row<T> tile{head_wait() + tile_off};
+                        inf_row_setup<T, NQ>(a, g, l, L, qc, tile, ver, delta, pv, tick_base, found, fb, pass_q);
 #pragma unroll
                         for (int k = 0; k < kLaneWin; ++k) { ymin[k] = CG_SY(L, k); prevw[k] = -INFINITY; }
                         pair_sync();
@@ -965,15 +991,15 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     }
 #pragma unroll 1
                     for (int u = 0; u < n_bk; ++u) {
-                        const T* rows = slot_wait(0);
+                        Row<T> tile{head_wait() + tile_off};
                         const int first = u * kRowsPerUse, nr = min(kRowsPerUse, B - 1 - first);
 #pragma unroll 1
                         for (int r = 0; r < nr; ++r) {
-                            CG_CHECK(4, (const unsigned char*)(rows + r * pitch + l.bt) >= smem &&
-                                        (const unsigned char*)(rows + r * pitch + l.bt + kTile) <= smem + (size_t)n_slots * a.slot_bytes &&
+                            CG_CHECK(4, tile.s >= ring_s && tile.s + kTile * sizeof(T) <= ring_s + (uint32_t)n_slots * a.slot_bytes &&
                                         first + r < B - 1);
-                            bucket_row<T, NQ>(a, g, l, L, rows + r * pitch + l.bt, first + r, ver, delta, pv, tick_base,
+                            bucket_row<T, NQ>(a, g, l, L, tile, first + r, ver, delta, pv, tick_base,
                                               prevw, ymin, found, fb, pass_q, any);
+                            tile.s += a.row_bytes;
                         }
                         pair_sync();
                         slot_release();
