@@ -160,12 +160,19 @@ struct SlotGeom {
 
 struct SlotTerms { int i0, n4; double f, gchk, dstart, endt, rinv; };
 
+// first sample of the window of tick j (any integer, also negative)
+CG_DEVINL int slot_first_sample(const WarpArgs& a, int32_t phase, int j) {
+    const cg_params& p = a.p;
+    const int lo = p.tick0_ms + j * p.tick_step_ms - p.window_ms;
+    return p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+}
+
 // Appendix A step 3 and 5 for the 4-sample window of tick j (any integer, also negative).
 CG_DEVINL SlotTerms slot_terms(const WarpArgs& a, int32_t phase, int j) {
     const cg_params& p = a.p;
     SlotTerms r;
     const int t = p.tick0_ms + j * p.tick_step_ms, lo = t - p.window_ms;
-    const int i0 = p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+    const int i0 = slot_first_sample(a, phase, j);
     const int i1 = floor_div32(t - phase, p.period_ms);
     r.i0 = i0;
     r.n4 = (i1 - i0 + 1 == 4) ? 1 : 0;
@@ -712,6 +719,20 @@ CG_DEVINL FillEntry fill_entry(const WarpArgs& a, int u) {
 
 // ---- warp-cooperative exact evaluation of one (pair, version, tick) from global memory: the
 // plain sequential semantics (tick_geom, series_increase, bucketQuantile), two buckets per lane.
+// one out-of-line copy of the window walk for the three places below (this path is cold; small code matters more)
+template <typename T>
+__device__ __noinline__ double series_increase_cold(const T* __restrict__ row, const TickGeom& g) {
+    double first_v = (double)row[g.i0];
+    double result = (double)row[g.i0 + g.n - 1] - first_v, prev = first_v;
+#pragma unroll 1
+    for (int i = 1; i < g.n; ++i) {
+        const double v = (double)row[g.i0 + i];
+        if (v < prev) result += prev;      // counter reset
+        prev = v;
+    }
+    return extrapolate(result, first_v, g);
+}
+
 template <typename T>
 __device__ __noinline__ void coop_eval_tick(const WarpArgs& a, int64_t pv, int32_t phase, int tick, int lane,
                                             double* m, uint8_t& valid_out) {
@@ -726,7 +747,7 @@ __device__ __noinline__ void coop_eval_tick(const WarpArgs& a, int64_t pv, int32
     unsigned have = 0;
     if (g.n >= 2) {
         double mine = 0.0;
-        if (lane < K) mine = series_increase(sc + (size_t)lane * p.row_pitch, g);
+        if (lane < K) mine = series_increase_cold<T>(sc + (size_t)lane * p.row_pitch, g);
         for (int k = 0; k < K; ++k) {
             const double inc = __shfl_sync(kFullMask, mine, k);
             const unsigned role = p.scalar_role[k];
@@ -756,8 +777,8 @@ __device__ __noinline__ void coop_eval_tick(const WarpArgs& a, int64_t pv, int32
         }
         if (scan) {   // B <= 64 (eligibility test): lane l holds buckets l and l+32
             double v0 = -INFINITY, v1 = -INFINITY;
-            if (lane < B) v0 = ddiv_call(series_increase(bk + (size_t)lane * p.row_pitch, g), range_s);
-            if (lane + 32 < B) v1 = ddiv_call(series_increase(bk + (size_t)(lane + 32) * p.row_pitch, g), range_s);
+            if (lane < B) v0 = ddiv_call(series_increase_cold<T>(bk + (size_t)lane * p.row_pitch, g), range_s);
+            if (lane + 32 < B) v1 = ddiv_call(series_increase_cold<T>(bk + (size_t)(lane + 32) * p.row_pitch, g), range_s);
             for (int d = 1; d < 32; d <<= 1) {        // running max in bucket order (monotonic fix)
                 const double o0 = __shfl_up_sync(kFullMask, v0, d), o1 = __shfl_up_sync(kFullMask, v1, d);
                 if (lane >= d && o0 > v0) v0 = o0;
@@ -807,7 +828,7 @@ __device__ __forceinline__ void warp_geometry(const WarpArgs& a, int32_t phase, 
     const bool phase_ok = phase > -(1 << 30) && phase < (1 << 30);
     SlotTerms t;
     t.i0 = 1; t.n4 = 0; t.f = 0.0; t.gchk = 1.0; t.dstart = 0.0; t.endt = 0.0; t.rinv = 0.0;
-    if (lane < 3 && phase_ok) t = slot_terms(a, phase, chunk0 - lane);
+    if (lane < 3 && phase_ok) t.i0 = slot_first_sample(a, phase, chunk0 - lane);
     const unsigned even = __ballot_sync(kFullMask, lane < 3 && !(t.i0 & 1));
     const int c = even ? __ffs(even) - 1 : 0;
     const int j0 = chunk0 - c;
