@@ -144,6 +144,7 @@ CG_DEVINL int floor_div32(int a, int b) {   // b > 0
     int q = a / b;
     return (a % b != 0 && a < 0) ? q - 1 : q;
 }
+CG_DEVNOINL int floor_div32_call(int a, int b) { return floor_div32(a, b); }   // one copy where speed does not matter
 CG_DEVINL TickGeom tick_geom32(const cg_params& p, int32_t phase, int tick) {
     TickGeom g;
     const int t  = p.tick0_ms + tick * p.tick_step_ms;

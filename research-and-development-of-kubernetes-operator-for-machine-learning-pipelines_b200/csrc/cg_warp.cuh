@@ -164,7 +164,7 @@ struct SlotTerms { int i0, n4; double f, gchk, dstart, endt, rinv; };
 CG_DEVINL int slot_first_sample(const WarpArgs& a, int32_t phase, int j) {
     const cg_params& p = a.p;
     const int lo = p.tick0_ms + j * p.tick_step_ms - p.window_ms;
-    return p.left_open ? floor_div32(lo - phase, p.period_ms) + 1 : -floor_div32(phase - lo, p.period_ms);
+    return p.left_open ? floor_div32_call(lo - phase, p.period_ms) + 1 : -floor_div32_call(phase - lo, p.period_ms);
 }
 
 // Appendix A step 3 and 5 for the 4-sample window of tick j (any integer, also negative).
@@ -173,7 +173,7 @@ CG_DEVINL SlotTerms slot_terms(const WarpArgs& a, int32_t phase, int j) {
     SlotTerms r;
     const int t = p.tick0_ms + j * p.tick_step_ms, lo = t - p.window_ms;
     const int i0 = slot_first_sample(a, phase, j);
-    const int i1 = floor_div32(t - phase, p.period_ms);
+    const int i1 = floor_div32_call(t - phase, p.period_ms);
     r.i0 = i0;
     r.n4 = (i1 - i0 + 1 == 4) ? 1 : 0;
     r.f = 0.0; r.gchk = 1.0; r.dstart = 0.0; r.endt = 0.0; r.rinv = 0.0;
@@ -779,6 +779,7 @@ __device__ __noinline__ void coop_eval_tick(const WarpArgs& a, int64_t pv, int32
             double v0 = -INFINITY, v1 = -INFINITY;
             if (lane < B) v0 = ddiv_call(series_increase_cold<T>(bk + (size_t)lane * p.row_pitch, g), range_s);
             if (lane + 32 < B) v1 = ddiv_call(series_increase_cold<T>(bk + (size_t)(lane + 32) * p.row_pitch, g), range_s);
+#pragma unroll 1
             for (int d = 1; d < 32; d <<= 1) {        // running max in bucket order (monotonic fix)
                 const double o0 = __shfl_up_sync(kFullMask, v0, d), o1 = __shfl_up_sync(kFullMask, v1, d);
                 if (lane >= d && o0 > v0) v0 = o0;
@@ -949,9 +950,13 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         if (!hp) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
             if (tid == 0 && a.decisions) a.decisions[pair] = replay_schedule([](int) { return false; }, false, st_tick, p);
-            if (a.gate_bits) for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = 0u;
+            if (a.gate_bits) {
+#pragma unroll 1
+                for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = 0u;
+            }
             continue;
         }
+#pragma unroll 1
         for (int w = tid; w < 2 * n_words; w += kLanes) s_bits[w] = 0u;
         const int32_t phase0 = a.phase[pair * 2], phase1 = a.phase[pair * 2 + 1];
 #pragma unroll 1
@@ -1076,6 +1081,7 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     if (a.metrics) {
                         double* on = a.metrics + ((size_t)(pair * 2) * p.n_ticks + tick) * W;
                         double* oo = a.metrics + ((size_t)(pair * 2 + 1) * p.n_ticks + tick) * W;
+#pragma unroll 1
                         for (int c = 0; c < W; ++c) { on[c] = mn[c]; oo[c] = mo[c]; }
                     }
                     if (a.valid) {
@@ -1087,7 +1093,10 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         }
         pair_sync();
         // ---- the step loop (:296-361) over the pair's promote bits
-        if (a.gate_bits) for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = s_bits[w];
+        if (a.gate_bits) {
+#pragma unroll 1
+            for (int w = tid; w < n_words; w += kLanes) a.gate_bits[pair * n_words + w] = s_bits[w];
+        }
         if (tid == 0 && a.decisions) {
             const int st_tick = a.start_tick ? a.start_tick[pair] : p.start_tick;
             a.decisions[pair] = replay_schedule_bits(s_bits, n_words, true, st_tick, p);
