@@ -32,6 +32,8 @@ def _units():
         extra += [f"-DCG_MIN_CTAS={int(os.environ['CG_MIN_CTAS'])}"]
     if os.environ.get("CG_ROWS_PER_USE"):            # developer build: rows per ring slot
         extra += [f"-DCG_ROWS_PER_USE={int(os.environ['CG_ROWS_PER_USE'])}"]
+    if os.environ.get("CG_MAXNREG"):                 # developer build: explicit register cap instead of a CTA count
+        extra += [f"-DCG_MAXNREG={int(os.environ['CG_MAXNREG'])}"]
     if os.environ.get("CG_G"):                       # developer build: periods of the tick grid per lane (1, 2 or 4)
         extra += [f"-DCG_G={int(os.environ['CG_G'])}"]
     units = [("cg_api", "cg_api.cu", extra)]

@@ -867,8 +867,13 @@ __device__ __forceinline__ void pair_sync() {
 #ifndef CG_MIN_CTAS
 #define CG_MIN_CTAS (kG == 4 ? 7 : kG == 2 ? 8 : 4)
 #endif
+#ifdef CG_MAXNREG
+#define CG_REG_BUDGET __maxnreg__(CG_MAXNREG)      // developer build: explicit register cap
+#else
+#define CG_REG_BUDGET __launch_bounds__(kLanes, CG_MIN_CTAS)
+#endif
 template <typename T, int NQ>
-__global__ void __launch_bounds__(kLanes, CG_MIN_CTAS)
+__global__ void CG_REG_BUDGET
 warp_kernel(const __grid_constant__ WarpArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const cg_params& p = a.p;

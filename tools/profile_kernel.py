@@ -12,7 +12,8 @@ from canary_b200 import engine, params as P, synth  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 path = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-p = P.make_params()
+n_samples = int(sys.argv[4]) if len(sys.argv) > 4 else 240      # shorter series: less shared memory per CTA
+p = P.make_params(n_samples=n_samples, n_ticks=(n_samples * 15 - 60) // 10 + 1) if n_samples != 240 else P.make_params()
 le = torch.from_numpy(synth.default_le(p.n_buckets)).cuda()
 sc, bk, ph = engine.synth_fill(n, p, le, seed=0xC0FFEE + 3)
 torch.cuda.synchronize()
