@@ -34,6 +34,8 @@ def _units():
         extra += [f"-DCG_ROWS_PER_USE={int(os.environ['CG_ROWS_PER_USE'])}"]
     if os.environ.get("CG_MAXNREG"):                 # developer build: explicit register cap instead of a CTA count
         extra += [f"-DCG_MAXNREG={int(os.environ['CG_MAXNREG'])}"]
+    if os.environ.get("CG_DEFS"):                    # developer build: experimental switches, comma separated
+        extra += [f"-D{d}" for d in os.environ["CG_DEFS"].split(",") if d]
     if os.environ.get("CG_G"):                       # developer build: periods of the tick grid per lane (1, 2 or 4)
         extra += [f"-DCG_G={int(os.environ['CG_G'])}"]
     units = [("cg_api", "cg_api.cu", extra)]

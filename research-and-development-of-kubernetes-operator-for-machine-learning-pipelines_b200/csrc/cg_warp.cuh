@@ -625,6 +625,12 @@ CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, 
     }
 }
 
+template <typename T, int NQ, typename AnyFn>
+CG_DEVINL void bucket_row_x(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, const double (&x)[kTile],
+                            const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
+                            double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
+                            unsigned& pass_bits, AnyFn any);
+
 // one bucket row in window space; prevw = running maxima of the window deltas (monotonic fix),
 // ymin = smallest delta that may reach a rank still searched
 template <typename T, int NQ, typename AnyFn>
@@ -632,8 +638,18 @@ CG_DEVINL void bucket_row(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, con
                           const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
                           double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
                           unsigned& pass_bits, AnyFn any) {
-    double x[kTile], w[kLaneWin];
+    double x[kTile];
     TileLoad<T>::load(tile.ptr(), x);
+    bucket_row_x<T, NQ>(a, g, lg, L, x, tile, b, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_bits, any);
+}
+
+// the same with the tile already in registers
+template <typename T, int NQ, typename AnyFn>
+CG_DEVINL void bucket_row_x(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, const double (&x)[kTile],
+                            const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
+                            double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
+                            unsigned& pass_bits, AnyFn any) {
+    double w[kLaneWin];
     window_deltas(x, w);
     const double gmin = g.gmin;
     bool cflag;
@@ -1024,6 +1040,16 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     for (int u = 0; u < n_bk; ++u) {
                         Row<T> tile{head_wait() + tile_off};
                         const int first = u * kRowsPerUse, nr = min(kRowsPerUse, B - 1 - first);
+#ifdef CG_PREFETCH2
+                        if (kRowsPerUse == 2 && nr == 2) {          // both tiles of the slot in flight before the first is used
+                            double xa[kTile], xb[kTile];
+                            const Row<T> tile2{tile.s + a.row_bytes};
+                            TileLoad<T>::load(tile.ptr(), xa);
+                            TileLoad<T>::load(tile2.ptr(), xb);
+                            bucket_row_x<T, NQ>(a, g, l, L, xa, tile, first, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_q, any);
+                            bucket_row_x<T, NQ>(a, g, l, L, xb, tile2, first + 1, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_q, any);
+                        } else
+#endif
 #pragma unroll 1
                         for (int r = 0; r < nr; ++r) {
                             CG_CHECK(4, tile.s >= ring_s && tile.s + kTile * sizeof(T) <= ring_s + (uint32_t)n_slots * a.slot_bytes &&
