@@ -1040,16 +1040,6 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
                     for (int u = 0; u < n_bk; ++u) {
                         Row<T> tile{head_wait() + tile_off};
                         const int first = u * kRowsPerUse, nr = min(kRowsPerUse, B - 1 - first);
-#ifdef CG_PREFETCH2
-                        if (kRowsPerUse == 2 && nr == 2) {          // both tiles of the slot in flight before the first is used
-                            double xa[kTile], xb[kTile];
-                            const Row<T> tile2{tile.s + a.row_bytes};
-                            TileLoad<T>::load(tile.ptr(), xa);
-                            TileLoad<T>::load(tile2.ptr(), xb);
-                            bucket_row_x<T, NQ>(a, g, l, L, xa, tile, first, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_q, any);
-                            bucket_row_x<T, NQ>(a, g, l, L, xb, tile2, first + 1, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_q, any);
-                        } else
-#endif
 #pragma unroll 1
                         for (int r = 0; r < nr; ++r) {
                             CG_CHECK(4, tile.s >= ring_s && tile.s + kTile * sizeof(T) <= ring_s + (uint32_t)n_slots * a.slot_bytes &&
