@@ -481,8 +481,9 @@ def main():
         e2e_inc = {"value": world * n / (inc_ms * 1e-3), "unit": UNIT, "ms_per_step": inc_ms, "steps": steps_i,
                    "h2d_bytes_per_step": n * 2 * (K + B) * p.elem_bytes, "d2h_bytes_per_step": n * 24,
                    "matches_oracle_on_sample": bool((out_i[sidx.cpu()].numpy() == want_i).all()),
-                   "api": "engine.RollingStore.append_scrape (one new scrape per series, pinned host -> HBM, cg_store_append) "
-                          "+ RollingStore.evaluate (cg_eval_fused over the newest hour) + decisions to pinned host memory"}
+                   "api": "engine.RollingStore.append_scrape (one new scrape per series, pinned host -> HBM on the store's copy "
+                          "stream, cg_store_append) + RollingStore.evaluate (cg_eval_fused over the newest hour) + decisions to "
+                          "pinned host memory; the upload of step j+1 overlaps the evaluation of step j"}
         del store, fresh_sc, fresh_bk
         torch.cuda.empty_cache()
 

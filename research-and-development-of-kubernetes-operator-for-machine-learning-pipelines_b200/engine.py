@@ -283,8 +283,13 @@ class RollingStore:
         self.scalars = self._sc[: self.n * 2 * K * self.cap].view(self.n, 2, K, self.cap)
         self.buckets = self._bk[: self.n * 2 * B * self.cap].view(self.n, 2, B, self.cap)
         self.phase = torch.zeros((self.n, 2), dtype=torch.int32, device=self.dev)
-        self._new_sc = torch.empty((self.n, 2, K), dtype=dt, device=self.dev)
-        self._new_bk = torch.empty((self.n, 2, B), dtype=dt, device=self.dev)
+        # two staging buffers and a copy stream: the upload of scrape j+1 overlaps the evaluation of scrape j
+        self._new_sc = [torch.empty((self.n, 2, K), dtype=dt, device=self.dev) for _ in range(2)]
+        self._new_bk = [torch.empty((self.n, 2, B), dtype=dt, device=self.dev) for _ in range(2)]
+        self._copy_stream = torch.cuda.Stream(device=self.dev)
+        self._ready = [torch.cuda.Event() for _ in range(2)]     # staging buffer filled (copy stream)
+        self._used = [None, None]                                # staging buffer consumed (caller's stream)
+        self._stage = 0
         self._phase_eff = torch.empty_like(self.phase)
         self.count = 0
         self.h2d_bytes = 0
@@ -304,7 +309,9 @@ class RollingStore:
         self.count = m
 
     def append_scrape(self, new_scalars: torch.Tensor, new_buckets: torch.Tensor):
-        """One new scrape of every series: [n, 2, K] and [n, 2, B], pinned host or device memory."""
+        """One new scrape of every series: [n, 2, K] and [n, 2, B], pinned host or device memory.
+        Host tensors are uploaded on the store's copy stream (they must stay untouched until the
+        caller's stream has passed this call); everything else is enqueued on the current stream."""
         p = self._pp
         if self.count == self.cap:                               # slack used up: the oldest samples fall off
             keep = self.T - 1
@@ -313,16 +320,33 @@ class RollingStore:
                                                self.count - keep, keep, _stream_ptr()), "cg_store_shift")
             self.count = keep
         self.h2d_bytes = 0
-        for src, dst in ((new_scalars, self._new_sc), (new_buckets, self._new_bk)):
-            if dst.numel():
-                dst.copy_(src, non_blocking=True)
-                if not src.is_cuda:
-                    self.h2d_bytes += src.numel() * src.element_size()
+        st = self._stage
+        self._stage ^= 1
+        cur = torch.cuda.current_stream(self.dev)
+        stage_sc, stage_bk = self._new_sc[st], self._new_bk[st]
+        from_host = any(t.numel() and not src.is_cuda for src, t in ((new_scalars, stage_sc), (new_buckets, stage_bk)))
+        side = self._copy_stream if from_host else cur
+        if from_host and self._used[st] is not None:
+            side.wait_event(self._used[st])                      # the append that last read this staging buffer
+        with torch.cuda.stream(side):
+            for src, dst in ((new_scalars, stage_sc), (new_buckets, stage_bk)):
+                if dst.numel():
+                    dst.copy_(src, non_blocking=True)
+                    if not src.is_cuda:
+                        self.h2d_bytes += src.numel() * src.element_size()
+            if from_host:
+                self._ready[st].record(side)
+        if from_host:
+            cur.wait_event(self._ready[st])
         _lib.check(_lib.lib.cg_store_append(_ptr(self.scalars if p.n_scalar else None),
                                             _ptr(self.buckets if p.n_buckets else None),
-                                            _ptr(self._new_sc if p.n_scalar else None),
-                                            _ptr(self._new_bk if p.n_buckets else None), self.n, C.byref(p),
+                                            _ptr(stage_sc if p.n_scalar else None),
+                                            _ptr(stage_bk if p.n_buckets else None), self.n, C.byref(p),
                                             self.count, _stream_ptr()), "cg_store_append")
+        if from_host:
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self._used[st] = ev
         self.count += 1
 
     def view(self):
