@@ -34,15 +34,21 @@ class SeriesStore:
 
     Rows are model pairs; `index[(deployment_name, namespace)] -> (row, {predictor_name:
     version})` plays the part of Prometheus' label index for the three labels every query
-    of the reference fixes (:367-410).  `now_ms` is the evaluation time of instant queries
-    (the reference uses the server's wall clock)."""
+    of the reference fixes (:367-410).  `now_ms` is the evaluation time of instant queries (the
+    reference uses the server's wall clock) in the STORE's time: milliseconds since `epoch_ms`,
+    the Unix time of the store's origin (0 for synthetic batches, the first time stamp for
+    ingested ones).  Device time is int32 milliseconds: `set_wall_time` converts a Unix time and
+    every evaluation refuses a time outside +-2^30 ms of the origin instead of wrapping."""
+
+    TIME_LIMIT_MS = 1 << 30
 
     def __init__(self, scalars: torch.Tensor, buckets: torch.Tensor, le: torch.Tensor,
                  phase: torch.Tensor, params: CgParams, index: Optional[Dict] = None,
-                 now_ms: Optional[int] = None):
+                 now_ms: Optional[int] = None, epoch_ms: int = 0):
         self.scalars, self.buckets, self.le, self.phase = scalars, buckets, le, phase
         self.params = params
         self.index: Dict[Tuple[str, str], Tuple[int, Dict[str, int]]] = index or {}
+        self.epoch_ms = int(epoch_ms)
         self.now_ms = params.tick0_ms if now_ms is None else now_ms
         self._cache: Dict[Tuple[int, int, int], tuple] = {}
 
@@ -56,13 +62,26 @@ class SeriesStore:
         dev = torch.device(device)
         t = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
         return cls(t(batch.scalars), t(batch.buckets), t(batch.le), t(batch.phase),
-                   batch.params, index=index, now_ms=now_ms)
+                   batch.params, index=index, now_ms=now_ms, epoch_ms=getattr(batch, "epoch_ms", 0) or 0)
 
     def register(self, deployment_name: str, namespace: str, row: int, new_version, old_version):
         self.index[(deployment_name, namespace)] = (row, {f"v{new_version}": 0, f"v{old_version}": 1})
 
     def set_time(self, now_ms: int):
+        """Evaluation time in the store's time (ms since `epoch_ms`)."""
         self.now_ms = int(now_ms)
+
+    def set_wall_time(self, unix_ms: int):
+        """Evaluation time as Unix milliseconds (what a Prometheus server would call now)."""
+        self.now_ms = int(unix_ms) - self.epoch_ms
+
+    def _device_now(self, elapsed_time) -> int:
+        """`now_ms` checked against the int32 range the kernels compute in."""
+        now, lim = int(self.now_ms), self.TIME_LIMIT_MS
+        if not (-lim < now - int(elapsed_time * 1000) and now < lim):
+            raise ValueError(f"evaluation time {now} ms is outside +-2^30 ms of the store's origin (epoch_ms = {self.epoch_ms}); "
+                             "pass store time, or use set_wall_time() for Unix time")
+        return now
 
     def advance(self, seconds: float):
         self.now_ms += int(round(seconds * 1000))
@@ -75,7 +94,7 @@ class SeriesStore:
             return hit
         p = self.params.copy()
         p.window_ms = int(elapsed_time * 1000)
-        p.tick0_ms = self.now_ms
+        p.tick0_ms = self._device_now(elapsed_time)
         p.n_ticks = 1
         metrics, valid = engine.eval_grid(self.scalars[row:row + 1], self.buckets[row:row + 1],
                                           self.le, self.phase[row:row + 1], p)
@@ -91,13 +110,14 @@ class IrregularSeriesStore(SeriesStore):
     layout).  get_model_metrics / should_promote_model / evaluate_canaries work on it unchanged."""
 
     def __init__(self, scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, params: CgParams,
-                 index: Optional[Dict] = None, now_ms: Optional[int] = None):
+                 index: Optional[Dict] = None, now_ms: Optional[int] = None, epoch_ms: int = 0):
         self.scalars, self.buckets, self.le = scalars, buckets, le
         self.ts_scalars, self.ts_buckets = ts_scalars, ts_buckets
         self.cnt_scalars, self.cnt_buckets = cnt_scalars, cnt_buckets
         self.phase = None
         self.params = params
         self.index = index or {}
+        self.epoch_ms = int(epoch_ms)
         self.now_ms = params.tick0_ms if now_ms is None else now_ms
         self._cache = {}
 
@@ -111,7 +131,8 @@ class IrregularSeriesStore(SeriesStore):
         t = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
         return cls(t(batch.scalars), t(batch.buckets), t(batch.ts_scalars), t(batch.ts_buckets),
                    t(batch.cnt_scalars), t(batch.cnt_buckets), t(batch.le), batch.params,
-                   index=index if index is not None else getattr(batch, "index", None), now_ms=now_ms)
+                   index=index if index is not None else getattr(batch, "index", None), now_ms=now_ms,
+                   epoch_ms=getattr(batch, "epoch_ms", 0) or 0)
 
     def _series(self, rows=slice(None)):
         return (self.scalars[rows], self.buckets[rows], self.ts_scalars[rows], self.ts_buckets[rows],
@@ -124,7 +145,7 @@ class IrregularSeriesStore(SeriesStore):
             return hit
         p = self.params.copy()
         p.window_ms = int(elapsed_time * 1000)
-        p.tick0_ms = self.now_ms
+        p.tick0_ms = self._device_now(elapsed_time)
         p.n_ticks = 1
         _, metrics, valid = engine.eval_irregular(*self._series(slice(row, row + 1)), p, want_metrics=True)
         out = (metrics[0, :, 0, :].cpu(), valid[0, :, 0].cpu(), p)
