@@ -57,16 +57,16 @@ __device__ __forceinline__ void mbar_arrive_expect_tx_s(uint32_t bar_s, uint32_t
 }
 
 __device__ __forceinline__ void mbar_wait_s(uint32_t bar_s, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(bar_s), "r"(parity)
-            : "memory");
-    } while (!ok);
+    // the loop lives in the PTX block (labels are local to it): test, leave, or try again
+    asm volatile(
+        "{\n\t.reg .pred p;\n"
+        "CG_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra CG_DONE;\n\t"
+        "bra CG_WAIT;\n"
+        "CG_DONE:\n\t}"
+        ::"r"(bar_s), "r"(parity)
+        : "memory");
 }
 
 __device__ __forceinline__ void bulk_g2s_s(uint32_t dst_s, const void* gmem_src, uint32_t bytes, uint32_t bar_s) {

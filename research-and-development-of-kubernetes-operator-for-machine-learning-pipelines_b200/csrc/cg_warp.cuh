@@ -947,8 +947,8 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, ring_s + (uint32_t)s * a.slot_bytes, bars_s + 8u * (uint32_t)s);
         cursor_next(fill);
     }
-    // oldest slot in use: index, shared addresses of its rows and of its mbarrier, parity of that mbarrier
-    uint32_t head = 0, head_parity = 0, head_s = ring_s, head_bar = bars_s;
+    // oldest slot in use: its index and the parity of its mbarrier
+    uint32_t head = 0, head_parity = 0;
     auto slot_wait = [&](int i) -> uint32_t {     // i-th slot from the head; returns the shared address of its rows
         uint32_t s = head + (uint32_t)i, par = head_parity;
         if (s >= (uint32_t)n_slots) { s -= n_slots; par ^= 1u; }
@@ -956,14 +956,15 @@ warp_kernel(const __grid_constant__ WarpArgs a) {
         return ring_s + s * a.slot_bytes;
     };
     auto head_wait = [&]() -> uint32_t {
-        mbar_wait_s(head_bar, head_parity);
-        return head_s;
+        mbar_wait_s(bars_s + 8u * head, head_parity);
+        return ring_s + head * a.slot_bytes;
     };
     auto slot_release = [&]() {                   // the head slot; callers have synchronised the pair's warps
-        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, head_s, head_bar);
+        if (tid == 0 && fill.pair < a.n_pairs) issue_fill(fill, ring_s + head * a.slot_bytes, bars_s + 8u * head);
         cursor_next(fill);
-        head_s += a.slot_bytes; head_bar += 8u;
-        if (++head == (uint32_t)n_slots) { head = 0; head_parity ^= 1u; head_s = ring_s; head_bar = bars_s; }
+        const bool wrap = ++head == (uint32_t)n_slots;
+        head = wrap ? 0u : head;
+        head_parity ^= wrap ? 1u : 0u;
     };
 
     for (int64_t pair = blockIdx.x; pair < a.n_pairs; pair += gridDim.x) {
