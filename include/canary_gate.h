@@ -234,7 +234,10 @@ int cg_store_shift(void* scalars, void* buckets, int64_t n_pairs, const cg_param
  * resident-tile kernel, 2 = the streaming kernel (CG_EINVAL if the geometry is not covered:
  * it needs window = 4 scrape periods and tick step = 2/3 period, the reference's constants
  * (:363, :294) with 15 s scrapes, at least 8 samples per series, at most 64 buckets and at
- * least one scalar series).  Both kernels give bit-identical results. */
+ * least one scalar series), 3 = the general row-streaming kernel (any window, tick grid and
+ * scrape period; rows must be a multiple of 16 bytes).  Automatic: 2 where it applies, else 3
+ * for grids of 32 ticks or more (or whenever decisions are asked for), else 1.  All kernels
+ * give bit-identical results. */
 int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const double* le,
                        const int32_t* phase, const uint8_t* has_previous, const int32_t* start_tick,
                        int64_t n_pairs, const cg_params* p, cg_decision* decisions,

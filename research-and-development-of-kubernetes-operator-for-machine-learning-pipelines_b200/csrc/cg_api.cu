@@ -10,6 +10,7 @@
 
 #include "../../include/canary_gate.h"
 #include "cg_general.cuh"
+#include "cg_rows.cuh"
 #include "cg_warp.cuh"
 #include "cg_irregular.cuh"
 #include "cg_synth.cuh"
@@ -120,6 +121,70 @@ int launch_general(const GeneralPlan& plan, cudaStream_t s) {
     kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "launch general_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
+// ---- row-streaming general kernel (cg_rows.cuh): eligibility, shared-memory plan, launch ------
+struct RowsPlan {
+    cg::RowsArgs args;
+    int grid, block;
+};
+
+int plan_rows(const cg_params* p, int64_t n_pairs, RowsPlan* plan, bool quiet) {
+    cg::RowsArgs& a = plan->args;
+    memset(&a, 0, sizeof(a));
+    a.p = *p;
+    a.n_pairs = n_pairs;
+    const size_t esz = elem_size(p), row_bytes = (size_t)p->row_pitch * esz;
+    const int rows = p->n_scalar + p->n_buckets;
+    if (row_bytes % 16 || row_bytes == 0 || rows < 1)
+        return quiet ? CG_EINVAL : fail(CG_EINVAL, "row-streaming kernel: a row must be a non-zero multiple of 16 bytes");
+    int g = (int)(16384 / row_bytes);           // about 16 KB per ring slot: a CTA barrier every 8 rows of an hour of scrapes
+    g = g < 1 ? 1 : (g > 16 ? 16 : g);
+    if (g > rows) g = rows;
+    const int slots = 3;
+    a.rows_per_slot = g;
+    a.n_slots = slots;
+    a.row_bytes = (uint32_t)row_bytes;
+    a.slot_bytes = (uint32_t)(g * row_bytes);
+    a.uses_per_ver = (rows + g - 1) / g;
+    int threads = ((p->n_ticks + 31) / 32) * 32;
+    threads = threads < 32 ? 32 : (threads > 384 ? 384 : threads);
+    plan->block = threads;
+    a.n_passes = (p->n_ticks + threads - 1) / threads;
+    size_t off = (size_t)slots * a.slot_bytes;
+    a.off_bars = (uint32_t)off;         off += (size_t)slots * 8;
+    off = (off + 15) & ~(size_t)15;
+    a.off_le = (uint32_t)off;           off += (size_t)p->n_buckets * 8;
+    a.off_stash = (uint32_t)off;        off += (size_t)p->n_ticks * 3 * 8;
+    a.off_stash_valid = (uint32_t)off;  off += ((size_t)p->n_ticks + 7) & ~(size_t)7;
+    a.off_bits = (uint32_t)off;         off += (((size_t)p->n_ticks + 31) / 32) * 4;
+    off = (off + 15) & ~(size_t)15;
+    if (off > (size_t)kMaxSmem || a.slot_bytes >= (1u << 20))
+        return quiet ? CG_EINVAL : fail(CG_EINVAL, "row-streaming kernel: ring and per-tick state need %zu bytes of shared memory (limit %d)", off, kMaxSmem);
+    a.smem_bytes = (uint32_t)off;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int per_sm = (int)((kMaxSmem + 1024) / (off + 1024));
+    per_sm = per_sm < 1 ? 1 : per_sm;
+    const int by_threads = 768 / threads;       // two CTAs of 384 threads by registers (__launch_bounds__(384, 2))
+    if (per_sm > by_threads) per_sm = by_threads < 1 ? 1 : by_threads;
+    int64_t gr = (int64_t)sms * per_sm;
+    if (gr > n_pairs) gr = n_pairs;
+    if (gr < 1) gr = 1;
+    plan->grid = (int)gr;
+    return CG_OK;
+}
+
+template <typename T>
+int launch_rows(const RowsPlan& plan, cudaStream_t s) {
+    auto kern = cg::rows_kernel<T>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.args.smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(rows_kernel)");
+    kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch rows_kernel");
     g_launches.fetch_add(1);
     return CG_OK;
 }
@@ -276,7 +341,7 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
     if ((rc = check_aligned(buckets, "buckets"))) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     // per-tick metric output alone (cg_eval_grid) also streams once the grid is worth a CTA
-    if ((decisions || p->n_ticks >= 32) && path != 1 && stream_eligible(p)) {
+    if ((decisions || p->n_ticks >= 32) && path != 1 && path != 3 && stream_eligible(p)) {
         StreamPlan sp;
         if ((rc = plan_stream(p, n_pairs, &sp))) return rc;
         cg::WarpArgs& a = sp.args;
@@ -286,6 +351,20 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
         return launch_stream(sp, s);
     }
     if (path == 2) return fail(CG_EINVAL, "geometry not covered by the streaming kernel");
+    // any other geometry: the rows pass through a ring (cg_rows.cuh) once the grid is worth a CTA;
+    // the resident-tile kernel keeps tiny grids and is the explicit path 1
+    if (path == 3 || (path == 0 && (decisions || p->n_ticks >= 32))) {
+        RowsPlan rp;
+        rc = plan_rows(p, n_pairs, &rp, path != 3);
+        if (rc == CG_OK) {
+            cg::RowsArgs& a = rp.args;
+            a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
+            a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
+            a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
+            return p->dtype == CG_F32 ? launch_rows<float>(rp, s) : launch_rows<double>(rp, s);
+        }
+        if (path == 3) return rc;
+    }
     GeneralPlan plan;
     if ((rc = plan_general(p, n_pairs, &plan))) return rc;
     cg::GeneralArgs& a = plan.args;
@@ -416,7 +495,7 @@ int cg_eval_fused_path(int path, const void* scalars, const void* buckets, const
                        int64_t n_pairs, const cg_params* p, cg_decision* decisions, uint32_t* gate_bits,
                        double* metrics, uint8_t* valid, void* stream) {
     if (n_pairs > 0 && !decisions) return fail(CG_EINVAL, "decisions is NULL");
-    if (path < 0 || path > 2) return fail(CG_EINVAL, "path must be 0 (auto), 1 (general) or 2 (streaming)");
+    if (path < 0 || path > 3) return fail(CG_EINVAL, "path must be 0 (auto), 1 (resident tile), 2 (streaming) or 3 (row streaming)");
     return run_general(scalars, buckets, le, phase, has_previous, start_tick, n_pairs, p, decisions,
                        gate_bits, metrics, valid, stream, path);
 }
@@ -575,6 +654,13 @@ int cg_launch_info(const cg_params* p, int64_t n_pairs, int32_t* grid, int32_t* 
         if (grid) *grid = sp.grid;
         if (block) *block = cg::kLanes;
         if (smem_bytes) *smem_bytes = (int32_t)sp.args.smem_bytes;
+        return CG_OK;
+    }
+    RowsPlan rp;
+    if (p->n_ticks >= 32 && plan_rows(p, n_pairs, &rp, true) == CG_OK) {
+        if (grid) *grid = rp.grid;
+        if (block) *block = rp.block;
+        if (smem_bytes) *smem_bytes = (int32_t)rp.args.smem_bytes;
         return CG_OK;
     }
     GeneralPlan plan;

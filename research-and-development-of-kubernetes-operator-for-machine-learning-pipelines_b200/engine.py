@@ -101,7 +101,7 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
                want_bits: bool = False, want_metrics: bool = False, out=None, path: int = 0):
     """metrics -> gate -> step loop in one pass over the series (mlflow_operator.py:302-317
     for every MlflowModel at once).  -> decisions [N, 6] int32 (+ gate_bits, metrics, valid).
-    path: 0 = let the library choose, 1 = general kernel, 2 = streaming kernel."""
+    path: 0 = let the library choose, 1 = resident-tile kernel, 2 = streaming kernel, 3 = row-streaming kernel."""
     n = _check_series(scalars, buckets, le, phase, p)
     dev = phase.device
     if has_previous is not None:

@@ -109,6 +109,13 @@ CONFIGS = {
     "ragged_pitch": dict(make=dict(n_samples=101, row_pitch=104, n_buckets=10), n=33, gen=dict(adversarial=0.1)),
     "long_window_30s_scrape": dict(make=dict(period_ms=30000, elapsed_time=300, n_samples=120, n_buckets=8,
                                              tick_step_ms=10000), n=40, gen={}),
+    # other scrape periods / windows / tick steps: the row-streaming kernel (path 3) is what runs them
+    "scrape_10s": dict(make=dict(period_ms=10000, n_samples=200, n_buckets=20), n=48, gen=dict(adversarial=0.1)),
+    "scrape_5s_window_30s_tick_20s": dict(make=dict(period_ms=5000, elapsed_time=30, n_samples=300, n_buckets=12,
+                                                    tick_step_ms=20000, attempt_delay_s=20), n=32, gen=dict(adversarial=0.1)),
+    "scrape_30s_three_quantiles_500_ticks": dict(make=dict(period_ms=30000, elapsed_time=120, n_samples=180, n_buckets=24,
+                                                           quantiles=(0.5, 0.9, 0.99), gate_q=2, n_ticks=500), n=24,
+                                                 gen=dict(adversarial=0.1)),
     "short_series": dict(make=dict(n_samples=6, n_buckets=4, n_ticks=40), n=17, gen=dict(resets=False)),
     "one_sample": dict(make=dict(n_samples=2, row_pitch=2, n_buckets=2, n_ticks=12), n=5, gen=dict(resets=False)),
     # streaming-kernel corner cases
@@ -141,7 +148,9 @@ def test_seeded_batch_matches_oracle(name):
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what=name)
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    paths = [1, 2] if engine.stream_eligible(p) else [1]
+    paths = [1, 2, 3] if engine.stream_eligible(p) else [1, 3]
+    if (p.row_pitch * p.elem_bytes) % 16:
+        paths.remove(3)                      # the row-streaming kernel copies whole rows: 16-byte multiples
     assert engine.stream_eligible(p) == (name in STREAMING), name
     for path in paths:
         got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
@@ -158,7 +167,7 @@ def test_fp32_storage_matches_oracle_on_rounded_inputs():
     got_m, got_v = gpu_grid(b)
     assert_metrics_match(got_m, want_m, got_v, want_v, rtol=1e-6, exact=True, what="fp32")
     want_dec, want_bits = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, n_threads=8)
-    for path in (1, 2):
+    for path in (1, 2, 3):
         got_dec, got_bits, m2, v2 = gpu_fused_metrics(b, path=path)
         assert np.array_equal(got_bits, want_bits) and np.array_equal(got_dec, want_dec)
         assert_metrics_match(m2, want_m, v2, want_v, rtol=1e-6, exact=True, what=f"fp32 path {path}")
@@ -171,7 +180,7 @@ def test_start_ticks_has_previous_and_running_out_of_data():
     st = rng.integers(0, p.n_ticks + 5, size=50).astype(np.int32)
     hp = (rng.random(50) < 0.8).astype(np.uint8)
     want, _ = co.eval_fused(b.scalars, b.buckets, b.le, b.phase, p, has_previous=hp, start_tick=st)
-    for path in (1, 2):
+    for path in (1, 2, 3):
         got, _ = gpu_fused(b, has_previous=hp, start_tick=st, path=path)
         assert np.array_equal(got, want), path
     assert (got[hp == 0, 2] == P.STATE_NO_CANARY).all()
