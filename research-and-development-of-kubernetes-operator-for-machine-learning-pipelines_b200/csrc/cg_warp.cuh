@@ -625,12 +625,6 @@ CG_DEVINL void bucket_finish(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, 
     }
 }
 
-template <typename T, int NQ, typename AnyFn>
-CG_DEVINL void bucket_row_x(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, const double (&x)[kTile],
-                            const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
-                            double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
-                            unsigned& pass_bits, AnyFn any);
-
 // one bucket row in window space; prevw = running maxima of the window deltas (monotonic fix),
 // ymin = smallest delta that may reach a rank still searched
 template <typename T, int NQ, typename AnyFn>
@@ -638,18 +632,8 @@ CG_DEVINL void bucket_row(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, con
                           const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
                           double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
                           unsigned& pass_bits, AnyFn any) {
-    double x[kTile];
+    double x[kTile], w[kLaneWin];
     TileLoad<T>::load(tile.ptr(), x);
-    bucket_row_x<T, NQ>(a, g, lg, L, x, tile, b, ver, delta, pv, tick_base, prevw, ymin, found, fb, pass_bits, any);
-}
-
-// the same with the tile already in registers
-template <typename T, int NQ, typename AnyFn>
-CG_DEVINL void bucket_row_x(const WarpArgs& a, const SlotGeom& g, LaneGeo& lg, const Lane& L, const double (&x)[kTile],
-                            const Row<T> tile, int b, int ver, int delta, int64_t pv, int tick_base,
-                            double (&prevw)[kLaneWin], double (&ymin)[kLaneWin], uint64_t& found, unsigned& fb,
-                            unsigned& pass_bits, AnyFn any) {
-    double w[kLaneWin];
     window_deltas(x, w);
     const double gmin = g.gmin;
     bool cflag;
