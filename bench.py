@@ -217,6 +217,33 @@ def secondary_configs(dev, peak, n_main, seed):
     p3 = P.make_params(dtype=P.CG_F32)
     sc3, bk3, ph3 = engine.synth_fill(n_main, p3, le, seed=seed + 3, device=dev)
     entry("configs3_fp32_storage", n_main, p3, lambda: engine.eval_fused(sc3, bk3, le, ph3, p3))
+    # ... and the cold end-to-end path in that storage mode: half the bytes cross PCIe (same API and timed
+    # region as the headline `e2e`: pinned host series -> chunks -> kernel -> decisions in pinned host memory)
+    try:
+        import time as _time
+        dec3 = engine.eval_fused(sc3, bk3, le, ph3, p3)
+        pipe3 = engine.HostPipeline(p3, chunk_pairs=4096)
+        hs3 = torch.empty(sc3.shape, dtype=sc3.dtype, pin_memory=True)
+        hb3 = torch.empty(bk3.shape, dtype=bk3.dtype, pin_memory=True)
+        hp3 = torch.empty(ph3.shape, dtype=ph3.dtype, pin_memory=True)
+        hs3.copy_(sc3); hb3.copy_(bk3); hp3.copy_(ph3)
+        out3 = torch.empty((n_main, 6), dtype=torch.int32, pin_memory=True)
+        torch.cuda.synchronize()
+        pipe3.run(hs3, hb3, hp3, le, out3)                                   # warm-up
+        same3 = bool((out3.numpy() == dec3.cpu().numpy()).all())
+        steps3 = 2
+        t0 = _time.perf_counter()
+        for _ in range(steps3):
+            pipe3.run(hs3, hb3, hp3, le, out3)
+        torch.cuda.synchronize()
+        ms3 = 1e3 * (_time.perf_counter() - t0) / steps3
+        out["e2e_fp32_storage"] = {"pairs": n_main, "ms_per_step": ms3, "pairs_per_s": n_main / (ms3 * 1e-3),
+                                   "h2d_bytes_per_step": pipe3.h2d_bytes, "d2h_bytes_per_step": pipe3.d2h_bytes,
+                                   "matches_device_path": same3, "steps": steps3,
+                                   "note": "engine.HostPipeline.run with fp32 series: the cold upload at half the bytes"}
+        del hs3, hb3, hp3, pipe3
+    except Exception as e:  # noqa: BLE001
+        out["e2e_fp32_storage"] = {"error": str(e)[:200]}
     del sc3, bk3
     # irregular series (per-series time stamps): 4096 pairs of the full layout
     p4 = P.make_params()
