@@ -210,6 +210,18 @@ int cg_eval_irregular(const void* scalars, const void* buckets, const int32_t* t
                       cg_decision* decisions, uint32_t* gate_bits, double* metrics,
                       uint8_t* valid, void* stream);
 
+/* Same as cg_eval_irregular with an explicit kernel choice: path 0 = automatic, 1 = values and time
+ * stamps of a (pair, version) resident in shared memory (at most about 220 KB of them), 3 = rows
+ * and their time-stamp rows through a ring (any K + B).  Automatic: 3 for grids of 32 ticks or
+ * more or when the resident tile does not fit, else 1.  Both give bit-identical results.
+ * Replaces the same lines as cg_eval_irregular (:302-317). */
+int cg_eval_irregular_path(int path, const void* scalars, const void* buckets,
+                           const int32_t* ts_scalars, const int32_t* ts_buckets,
+                           const int32_t* cnt_scalars, const int32_t* cnt_buckets, const double* le,
+                           const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
+                           const cg_params* p, cg_decision* decisions, uint32_t* gate_bits,
+                           double* metrics, uint8_t* valid, void* stream);
+
 /* Benchmark / test utility with no counterpart in the reference: fill device arrays with
  * seeded synthetic series (SURVEY.md 8(d) model).  Values are a pure function of
  * (seed, pair_offset + local pair, version, series, sample), so shards agree. */

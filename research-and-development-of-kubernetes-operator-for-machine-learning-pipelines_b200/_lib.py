@@ -37,6 +37,7 @@ def _load():
     lib.cg_eval_fused_path.argtypes = [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp]
     lib.cg_stream_eligible.argtypes = [_vp]
     lib.cg_eval_irregular.argtypes = [_vp] * 9 + [_i64] + [_vp] * 6
+    lib.cg_eval_irregular_path.argtypes = [C.c_int] + [_vp] * 9 + [_i64] + [_vp] * 6
     lib.cg_launch_info.argtypes = [_vp, _i64, _vp, _vp, _vp]
     lib.cg_store_append.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, C.c_int32, _vp]
     lib.cg_store_shift.argtypes = [_vp, _vp, _i64, _vp, C.c_int32, C.c_int32, _vp]

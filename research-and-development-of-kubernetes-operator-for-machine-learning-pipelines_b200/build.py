@@ -18,7 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libcanarygate.so")
-HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_rows.cuh", "cg_warp.cuh", "cg_irregular.cuh", "cg_synth.cuh", "cg_store.cuh",
+HEADERS = ["cg_math.cuh", "cg_ptx.cuh", "cg_general.cuh", "cg_rows.cuh", "cg_warp.cuh", "cg_irregular.cuh", "cg_irows.cuh", "cg_synth.cuh", "cg_store.cuh",
            os.path.join(ROOT, "include", "canary_gate.h")]
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

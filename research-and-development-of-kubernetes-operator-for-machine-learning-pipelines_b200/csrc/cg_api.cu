@@ -13,6 +13,7 @@
 #include "cg_rows.cuh"
 #include "cg_warp.cuh"
 #include "cg_irregular.cuh"
+#include "cg_irows.cuh"
 #include "cg_synth.cuh"
 #include "cg_store.cuh"
 
@@ -420,6 +421,73 @@ int plan_irregular(const cg_params* p, int64_t n_pairs, IrregularPlan* plan) {
     return CG_OK;
 }
 
+struct IRowsPlan {
+    cg::IRowsArgs args;
+    int grid, block;
+};
+
+// row-streaming kernel for irregular series (cg_irows.cuh); quiet: no error text when it does not apply
+int plan_irows(const cg_params* p, int64_t n_pairs, IRowsPlan* plan, bool quiet) {
+    cg::IRowsArgs& a = plan->args;
+    memset(&a, 0, sizeof(a));
+    a.p = *p;
+    a.n_pairs = n_pairs;
+    const size_t esz = elem_size(p), vrow = (size_t)p->row_pitch * esz, trow = (size_t)p->row_pitch * 4;
+    const int rows = p->n_scalar + p->n_buckets;
+    if (p->row_pitch % 4 || vrow == 0 || rows < 1)
+        return quiet ? CG_EINVAL : fail(CG_EINVAL, "irregular series: row_pitch must be a non-zero multiple of 4 samples");
+    int g = (int)(16384 / (vrow + trow));       // about 16 KB per ring slot
+    g = g < 1 ? 1 : (g > 16 ? 16 : g);
+    if (g > rows) g = rows;
+    const int slots = 3;
+    a.rows_per_slot = g;
+    a.n_slots = slots;
+    a.vrow_bytes = (uint32_t)vrow;
+    a.trow_bytes = (uint32_t)trow;
+    a.slot_bytes = (uint32_t)(g * (vrow + trow));
+    a.uses_per_ver = (rows + g - 1) / g;
+    int threads = ((p->n_ticks + 31) / 32) * 32;
+    threads = threads < 32 ? 32 : (threads > 384 ? 384 : threads);
+    plan->block = threads;
+    a.n_passes = (p->n_ticks + threads - 1) / threads;
+    size_t off = (size_t)slots * a.slot_bytes;
+    a.off_bars = (uint32_t)off;         off += (size_t)slots * 8;
+    off = (off + 15) & ~(size_t)15;
+    a.off_cnt = (uint32_t)off;          off += (size_t)rows * 12;       // counts, first time stamps, search hints
+    off = (off + 7) & ~(size_t)7;
+    a.off_le = (uint32_t)off;           off += (size_t)p->n_buckets * 8;
+    a.off_stash = (uint32_t)off;        off += (size_t)p->n_ticks * 3 * 8;
+    a.off_stash_valid = (uint32_t)off;  off += ((size_t)p->n_ticks + 7) & ~(size_t)7;
+    a.off_bits = (uint32_t)off;         off += (((size_t)p->n_ticks + 31) / 32) * 4;
+    off = (off + 15) & ~(size_t)15;
+    if (off > (size_t)kMaxSmem || a.slot_bytes >= (1u << 20))
+        return quiet ? CG_EINVAL : fail(CG_EINVAL, "irregular series: ring and per-tick state need %zu bytes of shared memory (limit %d)", off, kMaxSmem);
+    a.smem_bytes = (uint32_t)off;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int per_sm = (int)((kMaxSmem + 1024) / (off + 1024));
+    per_sm = per_sm < 1 ? 1 : per_sm;
+    const int by_threads = 768 / threads;       // two CTAs of 384 threads by registers (__launch_bounds__(384, 2))
+    if (per_sm > by_threads) per_sm = by_threads < 1 ? 1 : by_threads;
+    int64_t gr = (int64_t)sms * per_sm;
+    if (gr > n_pairs) gr = n_pairs;
+    if (gr < 1) gr = 1;
+    plan->grid = (int)gr;
+    return CG_OK;
+}
+
+template <typename T>
+int launch_irows(const IRowsPlan& plan, cudaStream_t s) {
+    auto kern = cg::irows_kernel<T>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.args.smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(irows_kernel)");
+    kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "launch irows_kernel");
+    g_launches.fetch_add(1);
+    return CG_OK;
+}
+
 template <typename T>
 int launch_irregular(const IrregularPlan& plan, cudaStream_t s) {
     auto kern = cg::irregular_kernel<T>;
@@ -505,6 +573,16 @@ int cg_eval_irregular(const void* scalars, const void* buckets, const int32_t* t
                       const double* le, const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
                       const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
                       uint8_t* valid, void* stream) {
+    return cg_eval_irregular_path(0, scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, has_previous,
+                                  start_tick, n_pairs, p, decisions, gate_bits, metrics, valid, stream);
+}
+
+int cg_eval_irregular_path(int path, const void* scalars, const void* buckets, const int32_t* ts_scalars,
+                           const int32_t* ts_buckets, const int32_t* cnt_scalars, const int32_t* cnt_buckets,
+                           const double* le, const uint8_t* has_previous, const int32_t* start_tick, int64_t n_pairs,
+                           const cg_params* p, cg_decision* decisions, uint32_t* gate_bits, double* metrics,
+                           uint8_t* valid, void* stream) {
+    if (path != 0 && path != 1 && path != 3) return fail(CG_EINVAL, "path must be 0 (auto), 1 (resident tile) or 3 (row streaming)");
     int rc = check_params(p);
     if (rc) return rc;
     if (n_pairs < 0) return fail(CG_EINVAL, "n_pairs < 0");
@@ -520,7 +598,23 @@ int cg_eval_irregular(const void* scalars, const void* buckets, const int32_t* t
     if ((int64_t)p->tick0_ms + (int64_t)p->n_ticks * p->tick_step_ms >= (1ll << 31) ||
         (int64_t)p->tick0_ms - p->window_ms <= -(1ll << 31))
         return fail(CG_EINVAL, "irregular series: tick times must fit int32 milliseconds");
+    // the rows through a ring once the grid is worth a CTA (and whenever the resident tile would not fit)
     IrregularPlan plan;
+    const bool tile_fits = path != 3 && plan_irregular(p, n_pairs, &plan) == CG_OK;
+    if (path == 3 || (path == 0 && (p->n_ticks >= 32 || !tile_fits))) {
+        IRowsPlan rp;
+        rc = plan_irows(p, n_pairs, &rp, path != 3 && tile_fits);
+        if (rc == CG_OK) {
+            cg::IRowsArgs& ra = rp.args;
+            ra.scalars = scalars; ra.buckets = buckets; ra.ts_scalars = ts_scalars; ra.ts_buckets = ts_buckets;
+            ra.cnt_scalars = cnt_scalars; ra.cnt_buckets = cnt_buckets; ra.le = le;
+            ra.has_previous = has_previous; ra.start_tick = start_tick; ra.decisions = decisions;
+            ra.gate_bits = gate_bits; ra.metrics = metrics; ra.valid = valid;
+            return p->dtype == CG_F32 ? launch_irows<float>(rp, (cudaStream_t)stream)
+                                      : launch_irows<double>(rp, (cudaStream_t)stream);
+        }
+        if (path == 3 || !tile_fits) return rc;
+    }
     if ((rc = plan_irregular(p, n_pairs, &plan))) return rc;
     cg::IrregularArgs& a = plan.args;
     a.scalars = scalars; a.buckets = buckets; a.ts_scalars = ts_scalars; a.ts_buckets = ts_buckets;

@@ -131,10 +131,12 @@ def eval_fused(scalars, buckets, le, phase, p: CgParams, has_previous=None, star
 
 
 def eval_irregular(scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_buckets, le, p: CgParams,
-                   has_previous=None, start_tick=None, want_bits: bool = False, want_metrics: bool = False):
+                   has_previous=None, start_tick=None, want_bits: bool = False, want_metrics: bool = False,
+                   path: int = 0):
     """The fused step for irregular series: every series has its own int32 ms
     time stamps `ts_*[N, 2, K|B, pitch]` and sample count `cnt_*[N, 2, K|B]`; stale markers already
-    dropped (ingest.build_irregular_batch does it).  -> decisions [N, 6] (+ gate_bits, metrics, valid)."""
+    dropped (ingest.build_irregular_batch does it).  -> decisions [N, 6] (+ gate_bits, metrics, valid).
+    path: 0 = let the library choose, 1 = resident-tile kernel, 3 = row-streaming kernel."""
     n = int(cnt_scalars.shape[0])
     dev = cnt_scalars.device
     if dev.type != "cuda":
@@ -162,11 +164,11 @@ def eval_irregular(scalars, buckets, ts_scalars, ts_buckets, cnt_scalars, cnt_bu
         metrics = torch.empty((n, 2, p.n_ticks, p.metric_width), dtype=torch.float64, device=dev)
         valid = torch.empty((n, 2, p.n_ticks), dtype=torch.uint8, device=dev)
     nb = bool(p.n_buckets)
-    _lib.check(_lib.lib.cg_eval_irregular(_ptr(scalars), _ptr(buckets if nb else None), _ptr(ts_scalars),
-                                          _ptr(ts_buckets if nb else None), _ptr(cnt_scalars),
-                                          _ptr(cnt_buckets if nb else None), _ptr(le if nb else None),
-                                          _ptr(has_previous), _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits),
-                                          _ptr(metrics), _ptr(valid), _stream_ptr()), "cg_eval_irregular")
+    _lib.check(_lib.lib.cg_eval_irregular_path(int(path), _ptr(scalars), _ptr(buckets if nb else None), _ptr(ts_scalars),
+                                               _ptr(ts_buckets if nb else None), _ptr(cnt_scalars),
+                                               _ptr(cnt_buckets if nb else None), _ptr(le if nb else None),
+                                               _ptr(has_previous), _ptr(start_tick), n, C.byref(p), _ptr(dec), _ptr(bits),
+                                               _ptr(metrics), _ptr(valid), _stream_ptr()), "cg_eval_irregular")
     res = [dec]
     if want_bits:
         res.append(bits)

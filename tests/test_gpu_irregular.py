@@ -13,12 +13,12 @@ from oracle import c_oracle as co
 pytestmark = pytest.mark.gpu
 
 
-def gpu_irregular(ib, p, start_tick=None, has_previous=None):
+def gpu_irregular(ib, p, start_tick=None, has_previous=None, path=0):
     t = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
     dec, bits, m, v = engine.eval_irregular(t(ib.scalars), t(ib.buckets), t(ib.ts_scalars), t(ib.ts_buckets),
                                             t(ib.cnt_scalars), t(ib.cnt_buckets), t(ib.le), p,
                                             has_previous=t(has_previous), start_tick=t(start_tick),
-                                            want_bits=True, want_metrics=True)
+                                            want_bits=True, want_metrics=True, path=path)
     torch.cuda.synchronize()
     return dec.cpu().numpy(), bits.cpu().numpy().view(np.uint32), m.cpu().numpy(), v.cpu().numpy()
 
@@ -78,19 +78,21 @@ def test_irregular_batch_matches_oracle(name):
     want_dec, want_bits, want_m, want_v = co.eval_irregular(
         ib.scalars, ib.buckets, ib.ts_scalars, ib.ts_buckets, ib.cnt_scalars, ib.cnt_buckets, ib.le, p,
         has_previous=hp, start_tick=st, n_threads=8, want_metrics=True)
-    dec, bits, m, v = gpu_irregular(ib, p, start_tick=st, has_previous=hp)
-    assert_metrics_match(m, want_m, v, want_v, rtol=1e-6, exact=True, what=name)
-    assert np.array_equal(bits, want_bits), name
-    assert np.array_equal(dec, want_dec), name
+    for path in (0, 1, 3):                 # automatic, resident tile, rows through the ring
+        dec, bits, m, v = gpu_irregular(ib, p, start_tick=st, has_previous=hp, path=path)
+        assert_metrics_match(m, want_m, v, want_v, rtol=1e-6, exact=True, what=f"{name} path {path}")
+        assert np.array_equal(bits, want_bits), (name, path)
+        assert np.array_equal(dec, want_dec), (name, path)
 
 
 def test_grid_series_through_the_irregular_kernel_equal_the_grid_kernels():
     p = P.make_params(n_samples=120, n_buckets=16)
     b = synth.generate(p, 40, seed=12, adversarial=0.2)
     want_dec, want_bits, want_m, want_v = gpu_fused_metrics(b)
-    dec, bits, m, v = gpu_irregular(synth.as_irregular(b), p)
-    assert_metrics_match(m, want_m, v, want_v, rtol=1e-6, exact=True, what="grid via irregular")
-    assert np.array_equal(bits, want_bits) and np.array_equal(dec, want_dec)
+    for path in (1, 3):
+        dec, bits, m, v = gpu_irregular(synth.as_irregular(b), p, path=path)
+        assert_metrics_match(m, want_m, v, want_v, rtol=1e-6, exact=True, what=f"grid via irregular path {path}")
+        assert np.array_equal(bits, want_bits) and np.array_equal(dec, want_dec)
 
 
 def test_irregular_rejects_what_it_cannot_run():
@@ -100,11 +102,28 @@ def test_irregular_rejects_what_it_cannot_run():
         engine.eval_irregular(z(1, 2, 4, 6), z(1, 2, 2, 6), z(1, 2, 4, 6, dt=torch.int32), z(1, 2, 2, 6, dt=torch.int32),
                               z(1, 2, 4, dt=torch.int32), z(1, 2, 2, dt=torch.int32),
                               torch.tensor([1.0, float("inf")], dtype=torch.float64, device="cuda"), p)
-    big = P.make_params(n_samples=480, n_buckets=64)                           # values + stamps exceed shared memory
+    big = P.make_params(n_samples=480, n_buckets=64)           # values + stamps of a version exceed shared memory
+    args = (z(1, 2, 4, 480), z(1, 2, 64, 480), z(1, 2, 4, 480, dt=torch.int32),
+            z(1, 2, 64, 480, dt=torch.int32), z(1, 2, 4, dt=torch.int32), z(1, 2, 64, dt=torch.int32),
+            torch.cat([torch.arange(63, dtype=torch.float64), torch.tensor([float("inf")], dtype=torch.float64)]).cuda(), big)
     with pytest.raises(Exception, match="shared"):
-        engine.eval_irregular(z(1, 2, 4, 480), z(1, 2, 64, 480), z(1, 2, 4, 480, dt=torch.int32),
-                              z(1, 2, 64, 480, dt=torch.int32), z(1, 2, 4, dt=torch.int32), z(1, 2, 64, dt=torch.int32),
-                              torch.cat([torch.arange(63, dtype=torch.float64), torch.tensor([float("inf")], dtype=torch.float64)]).cuda(), big)
+        engine.eval_irregular(*args, path=1)                   # the resident tile cannot hold it ...
+    dec = engine.eval_irregular(*args)                         # ... the rows through the ring can
+    assert dec.shape == (1, 6)
+
+
+def test_layout_too_large_for_a_resident_tile_matches_the_oracle():
+    """2 hours of scrapes x 68 series: 392 KB of values and stamps per (pair, version); only the
+    row-streaming kernel runs it."""
+    p = P.make_params(n_samples=480, n_buckets=64)
+    grid = synth.generate(p, 6, seed=5, adversarial=0.2)
+    ib = synth.make_irregular(grid, seed=3, jitter_ms=2000, miss_prob=0.02)
+    want_dec, want_bits, want_m, want_v = co.eval_irregular(
+        ib.scalars, ib.buckets, ib.ts_scalars, ib.ts_buckets, ib.cnt_scalars, ib.cnt_buckets, ib.le, p,
+        n_threads=8, want_metrics=True)
+    dec, bits, m, v = gpu_irregular(ib, p)
+    assert_metrics_match(m, want_m, v, want_v, rtol=1e-6, exact=True, what="large layout")
+    assert np.array_equal(bits, want_bits) and np.array_equal(dec, want_dec)
 
 
 def test_ingested_irregular_answers_give_the_oracle_decisions():

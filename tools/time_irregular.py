@@ -32,9 +32,10 @@ def timed(fn, reps=3):
     return min(ev[i].elapsed_time(ev[i + 1]) for i in range(reps)), out
 
 
-ms_i, dec_i = timed(lambda: engine.eval_irregular(sc, bk, ts_s, ts_b, cnt_s, cnt_b, le, p))
 ms_g, dec_g = timed(lambda: engine.eval_fused(sc, bk, le, ph, p))
-assert torch.equal(dec_i, dec_g), "irregular and grid kernels disagree on grid series"
 bytes_i = n * (p.bytes_per_pair() + 2 * (p.n_scalar + p.n_buckets) * (p.row_pitch * 4 + 4))
-print(f"pairs={n} irregular {ms_i:.3f} ms ({n / ms_i * 1e3:.0f} pairs/s, {bytes_i / ms_i / 1e6:.0f} GB/s of values+stamps) "
-      f"| streaming {ms_g:.3f} ms ({n / ms_g * 1e3:.0f} pairs/s); decisions identical")
+for path, what in ((1, "resident tile"), (3, "rows through the ring")):
+    ms_i, dec_i = timed(lambda: engine.eval_irregular(sc, bk, ts_s, ts_b, cnt_s, cnt_b, le, p, path=path))
+    assert torch.equal(dec_i, dec_g), "irregular and grid kernels disagree on grid series"
+    print(f"pairs={n} irregular, {what}: {ms_i:.3f} ms ({n / ms_i * 1e3:.0f} pairs/s, {bytes_i / ms_i / 1e6:.0f} GB/s of values+stamps)")
+print(f"streaming kernel on the same series: {ms_g:.3f} ms ({n / ms_g * 1e3:.0f} pairs/s); decisions identical")
