@@ -178,9 +178,9 @@ int plan_rows(const cg_params* p, int64_t n_pairs, RowsPlan* plan, bool quiet) {
     return CG_OK;
 }
 
-template <typename T>
+template <typename T, int MQ>
 int launch_rows(const RowsPlan& plan, cudaStream_t s) {
-    auto kern = cg::rows_kernel<T>;
+    auto kern = cg::rows_kernel<T, MQ>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.args.smem_bytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(rows_kernel)");
     kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
@@ -362,7 +362,8 @@ int run_general(const void* scalars, const void* buckets, const double* le, cons
             a.scalars = scalars; a.buckets = buckets; a.le = le; a.phase = phase;
             a.has_previous = has_previous; a.start_tick = start_tick; a.decisions = decisions;
             a.gate_bits = gate_bits; a.metrics = metrics; a.valid = valid;
-            return p->dtype == CG_F32 ? launch_rows<float>(rp, s) : launch_rows<double>(rp, s);
+            if (p->n_q <= 1) return p->dtype == CG_F32 ? launch_rows<float, 1>(rp, s) : launch_rows<double, 1>(rp, s);
+            return p->dtype == CG_F32 ? launch_rows<float, CG_MAX_Q>(rp, s) : launch_rows<double, CG_MAX_Q>(rp, s);
         }
         if (path == 3) return rc;
     }

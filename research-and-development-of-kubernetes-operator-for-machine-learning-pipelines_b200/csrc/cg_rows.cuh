@@ -6,7 +6,7 @@
 // load, wait, compute, and HBM idles meanwhile (8 % of the copy peak); larger layouts do not fit at
 // all.  Here a ring slot holds a few rows (15 KB), a CTA needs about 55 KB whatever K + B is, two
 // CTAs of 12 warps fit an SM by registers, and the TMA bulk-copy engine refills a slot while the
-// others are read.  Measured on configs[3]: 747 GB/s against 526 GB/s (11 % / 8 % of the copy
+// others are read.  Measured on configs[3]: 843 GB/s against 526 GB/s (13 % / 8 % of the copy
 // peak): the thread-per-tick scan itself (about 200 k warp instructions per pair) is what limits it.
 //
 //   * One thread per tick (a CTA covers up to blockDim.x ticks per pass over the pair's rows; longer
@@ -50,11 +50,12 @@ struct RowsArgs {
 };
 
 // what one thread carries through the rows of one (pair, version) for its tick
+template <int MQ>                  // MQ: quantiles the instance has room for (1, or CG_MAX_Q)
 struct TickScan {
     double   sums[5];
     double   f;                    // ext / sampled without the zero-point clamp (0 when the window is empty)
     double   c_inf;                // rate of the +Inf bucket: the speculated observations
-    double   rank[CG_MAX_Q], cand[CG_MAX_Q];
+    double   rank[MQ], cand[MQ];
     double   prevc, mx;
     unsigned have;                 // roles that had a series
     unsigned search;               // quantiles that need the bucket scan
@@ -108,7 +109,7 @@ __device__ __forceinline__ double window_increase_flagged(uint32_t win_s, const 
     return result * f;
 }
 
-template <typename T>
+template <typename T, int MQ>
 __global__ void __launch_bounds__(384, 2) rows_kernel(const __grid_constant__ RowsArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const cg_params& p = a.p;
@@ -188,13 +189,13 @@ __global__ void __launch_bounds__(384, 2) rows_kernel(const __grid_constant__ Ro
                 const int off = live ? g.i0 + 1 - base : 0;                        // flag of sample i sits at bit i - base
                 const unsigned wmask = live ? (g.n > 32 ? 0xffffffffu : (1u << (g.n - 1)) - 1u) : 0u;
                 double gchk = 0.0;
-                TickScan sc;
+                TickScan<MQ> sc;
 #pragma unroll
                 for (int r = 0; r < 5; ++r) sc.sums[r] = 0.0;
                 sc.have = 0u; sc.search = 0u; sc.hit = 0u;
                 sc.f = 0.0; sc.c_inf = 0.0; sc.prevc = 0.0; sc.mx = 0.0;
 #pragma unroll
-                for (int q = 0; q < CG_MAX_Q; ++q) { sc.rank[q] = NAN; sc.cand[q] = NAN; }
+                for (int q = 0; q < MQ; ++q) { sc.rank[q] = NAN; sc.cand[q] = NAN; }
                 if (live) {                       // Appendix A steps 5-6 without the clamp, once per tick
                     double ext = g.sampled;
                     ext += (g.d_start < g.thr) ? g.d_start : g.avg / 2;
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(384, 2) rows_kernel(const __grid_constant__ Ro
                                 const unsigned todo = sc.search & ~sc.hit;
                                 if (todo) {
 #pragma unroll
-                                    for (int q = 0; q < CG_MAX_Q; ++q) {
+                                    for (int q = 0; q < MQ; ++q) {
                                         if (((todo >> q) & 1u) && c >= sc.rank[q]) {
                                             sc.hit |= 1u << q;
                                             if (b == 0 && s_le[0] <= 0) sc.cand[q] = s_le[0];          // step 6
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(384, 2) rows_kernel(const __grid_constant__ Ro
                             } else if (r == K) {  // the +Inf bucket: speculated observations, ranks (step 5)
                                 sc.c_inf = div_const(inc, range_s, rc_range);
 #pragma unroll
-                                for (int q = 0; q < CG_MAX_Q; ++q)
+                                for (int q = 0; q < MQ; ++q)
                                     if (q < nq) sc.rank[q] = p.q[q] * sc.c_inf;
                             } else {              // Q2..Q6: sum(increase(...)) per role (:375-410)
                                 const unsigned role = p.scalar_role[r];
@@ -292,7 +293,7 @@ __global__ void __launch_bounds__(384, 2) rows_kernel(const __grid_constant__ Ro
                         eval_tick_resident<T>(gsc, gbk, s_le, p, g, m, v);
                     } else {
 #pragma unroll
-                        for (int q = 0; q < CG_MAX_Q; ++q) {
+                        for (int q = 0; q < MQ; ++q) {
                             if (q >= nq) continue;
                             double r = NAN;
                             if (B > 0 && live) {
