@@ -477,9 +477,9 @@ int plan_irows(const cg_params* p, int64_t n_pairs, IRowsPlan* plan, bool quiet)
     return CG_OK;
 }
 
-template <typename T>
+template <typename T, int MQ>
 int launch_irows(const IRowsPlan& plan, cudaStream_t s) {
-    auto kern = cg::irows_kernel<T>;
+    auto kern = cg::irows_kernel<T, MQ>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.args.smem_bytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(irows_kernel)");
     kern<<<plan.grid, plan.block, plan.args.smem_bytes, s>>>(plan.args);
@@ -611,8 +611,9 @@ int cg_eval_irregular_path(int path, const void* scalars, const void* buckets, c
             ra.cnt_scalars = cnt_scalars; ra.cnt_buckets = cnt_buckets; ra.le = le;
             ra.has_previous = has_previous; ra.start_tick = start_tick; ra.decisions = decisions;
             ra.gate_bits = gate_bits; ra.metrics = metrics; ra.valid = valid;
-            return p->dtype == CG_F32 ? launch_irows<float>(rp, (cudaStream_t)stream)
-                                      : launch_irows<double>(rp, (cudaStream_t)stream);
+            cudaStream_t st = (cudaStream_t)stream;
+            if (p->n_q <= 1) return p->dtype == CG_F32 ? launch_irows<float, 1>(rp, st) : launch_irows<double, 1>(rp, st);
+            return p->dtype == CG_F32 ? launch_irows<float, CG_MAX_Q>(rp, st) : launch_irows<double, CG_MAX_Q>(rp, st);
         }
         if (path == 3 || !tile_fits) return rc;
     }

