@@ -57,18 +57,24 @@ __device__ bool irregular_increase(const T* __restrict__ v, const int32_t* __res
     // walk: O(1) for near-regular scrapes, O(gap) otherwise.
     int a = wt.n ? wt.a : (int)((float)(lo - t0) * inv);
     a = a < 0 ? 0 : (a > cnt ? cnt : a);
+    // (the hint is right for all but a few rows: each loop tests once and falls through; not unrolled)
+#pragma unroll 1
     while (a > 0 && !(left_open ? ts[a - 1] <= lo : ts[a - 1] < lo)) --a;
+#pragma unroll 1
     while (a < cnt && (left_open ? ts[a] <= lo : ts[a] < lo)) ++a;
     // b = last sample at or before the tick: start from the length of the previous row's window
     int b = a - 1 + (wt.n ? wt.n : 0);
     if (b > cnt - 1) b = cnt - 1;
+#pragma unroll 1
     while (b >= a && ts[b] > t) --b;
+#pragma unroll 1
     while (b + 1 < cnt && ts[b + 1] <= t) ++b;
     const int n = b - a + 1;
     if (n < 2) return false;                                   // step 1
     const double first_v = (double)v[a];
     double result = (double)v[b] - first_v;                    // step 2
     double prev = first_v;
+#pragma unroll 1
     for (int i = a + 1; i <= b; ++i) {
         const double x = (double)v[i];
         if (x < prev) result += prev;                          // counter reset
