@@ -44,6 +44,7 @@ struct WindowTerms {
     int a;                       // index of its first sample (search hint for the next row)
     double d_start, sampled, thr, half_avg, end_term;
     double f;                    // ext / sampled when the zero-point clamp does not fire
+    double gchk;                 // first_v * gchk >= result  ==>  the zero-point clamp cannot fire
 };
 
 // increase() of one series at one tick from its own time stamps (Appendix A steps 1-6, the same
@@ -94,14 +95,15 @@ __device__ bool irregular_increase(const T* __restrict__ v, const int32_t* __res
         ext += (wt.d_start < wt.thr) ? wt.d_start : wt.half_avg;
         ext += wt.end_term;
         wt.f = ext / wt.sampled;
+        wt.gchk = (wt.sampled / wt.d_start) * (1.0 - 1e-6);   // (d_start = 0: +Inf, or NaN: always the exact path)
         wt.first_t = first_t; wt.last_t = last_t; wt.n = n;
     }
     wt.a = a;
     if (result > 0 && first_v >= 0) {                          // step 4: the zero-point clamp
-        // d_zero = sampled * (first_v / result) < d_start is impossible when first_v * sampled exceeds
-        // d_start * result by more than the roundings involved: one comparison instead of a division
-        const double lhs = first_v * wt.sampled, rhs = (wt.d_start * result) * (1.0 + 1e-12);
-        if (!(lhs >= rhs && lhs < 1e300 && rhs > 1e-290)) {
+        // d_zero = sampled * (first_v / result) < d_start needs first_v * (sampled / d_start) < result: with gchk a
+        // slight under-estimate of sampled / d_start, first_v * gchk >= result proves that the clamp cannot fire
+        // (one multiply instead of a division; the streaming kernel's test)
+        if (!(first_v * wt.gchk >= result)) {
             const double d_zero = wt.sampled * (first_v / result);
             if (d_zero < wt.d_start) {
                 double ext = wt.sampled;
